@@ -1,0 +1,167 @@
+/*
+ * b200sort.h -- C ABI of libb200sort.so, the B200 (sm_100a) LSD radix sort that
+ * replaces the hot path of jgrodzki/radix_sort.
+ *
+ * The reference exposes the sort as a Rust trait method, not an FFI:
+ *     pub trait RadixSort<T: RadixDigits> { fn radix_sort(&mut self); }
+ *                                   (src/radix_sort/mod.rs:18-20, impl at :61-176)
+ * keyed by `RadixDigits::get_digit`  (src/radix_sort/radix_digits.rs:1-136).
+ * This header is the FFI layer a Rust `impl RadixSort<T> for [T]` binds to
+ * (see INTEGRATION.md for the extern "C" block and the build.rs).
+ *
+ * Conventions: plain C, no C++ or torch types; every entry point returns an
+ * int status (0 = ok) and never throws; the message for the calling thread's
+ * last failure is b200sort_last_error().  There is NO CPU fallback: without a
+ * CUDA device every compute entry point returns B200SORT_ERR_CUDA.
+ * All entry points are re-entrant: concurrent calls from several host threads
+ * on different buffers are safe (the reference's tests run that way under
+ * libtest, src/radix_sort/tests.rs).
+ */
+#ifndef B200SORT_H
+#define B200SORT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200SORT_VERSION 100 /* 0.1.0 */
+
+/* Built-in key kinds = the RadixDigits impls of radix_digits.rs:7-124.
+ * usize/isize (radix_digits.rs:47-53,95-101) are U64/I64 on 64-bit targets. */
+typedef enum b200sort_kind {
+    B200SORT_U8 = 0,   /* radix_digits.rs:7-13   */
+    B200SORT_U16 = 1,  /* radix_digits.rs:15-21  */
+    B200SORT_U32 = 2,  /* radix_digits.rs:23-29  */
+    B200SORT_U64 = 3,  /* radix_digits.rs:31-37  */
+    B200SORT_U128 = 4, /* radix_digits.rs:39-45  */
+    B200SORT_I8 = 5,   /* radix_digits.rs:55-61  */
+    B200SORT_I16 = 6,  /* radix_digits.rs:63-69  */
+    B200SORT_I32 = 7,  /* radix_digits.rs:71-77  */
+    B200SORT_I64 = 8,  /* radix_digits.rs:79-85  */
+    B200SORT_I128 = 9, /* radix_digits.rs:87-93  */
+    B200SORT_F32 = 10, /* radix_digits.rs:106-114 */
+    B200SORT_F64 = 11, /* radix_digits.rs:116-124 */
+    B200SORT_KIND_COUNT = 12
+} b200sort_kind;
+
+typedef enum b200sort_status {
+    B200SORT_OK = 0,
+    B200SORT_ERR_INVALID_ARG = 1,      /* null pointer, misaligned buffer, short workspace */
+    B200SORT_ERR_UNSUPPORTED_KIND = 2, /* a user-defined RadixDigits impl cannot run on a GPU */
+    B200SORT_ERR_CUDA = 3,             /* any CUDA runtime failure, incl. "no device" */
+    B200SORT_ERR_OOM = 4               /* device or pinned-host allocation failed */
+} b200sort_status;
+
+/* flags for the *_ex entry points */
+#define B200SORT_FLAG_NO_SKIP 1u /* run every digit pass even when a digit is constant */
+
+int b200sort_version(void);
+
+/* Message of the calling thread's last failing call ("" if none). */
+const char *b200sort_last_error(void);
+
+/* NUMBER_OF_DIGITS / size in bytes of a key kind (radix_digits.rs:8,16,...,117);
+ * 0 for an unknown kind. */
+size_t b200sort_key_bytes(int kind);
+
+/* Bytes of device workspace b200sort_keys_device needs for n keys of `kind`:
+ * the ping-pong buffer the reference allocates at mod.rs:71-83 (n * key bytes)
+ * plus histograms, bucket bases and look-back state. 0 for an unknown kind. */
+size_t b200sort_temp_bytes(size_t n, int kind);
+
+/* Device-resident sort: replaces the body of RadixSort::radix_sort
+ * (mod.rs:61-176) for keys already in HBM.  Sorts d_keys[0..n) in place
+ * (ascending in the order get_digit defines: Ord for integers, total_cmp for
+ * floats), asynchronously on `stream` (a cudaStream_t; NULL = default stream).
+ * d_tmp/tmp_bytes: workspace of at least b200sort_temp_bytes(n, kind) bytes,
+ * 256-byte aligned; contents are clobbered.  No host synchronisation, no
+ * allocation: safe to capture into a CUDA graph.  n == 0 is a no-op (the
+ * reference panics there, mod.rs:92; documented deviation). */
+int b200sort_keys_device(void *d_keys, void *d_tmp, size_t tmp_bytes, size_t n,
+                         int kind, void *stream);
+int b200sort_keys_device_ex(void *d_keys, void *d_tmp, size_t tmp_bytes, size_t n,
+                            int kind, void *stream, unsigned flags);
+
+/* Drop-in for `slice.radix_sort()` on a host slice (call sites
+ * tests.rs:30,...,166; main.rs:33): copies keys to the current device, sorts,
+ * copies back into `keys`, blocks until done.  Owns its device memory. */
+int b200sort_keys_host(void *keys, size_t n, int kind);
+
+/* Key-value records, key = field 0 of a `(K, V)` tuple (radix_digits.rs:126-136;
+ * call sites tests.rs:182, main.rs:112,123).  Stable.  rec_bytes is the whole
+ * record (8 for (u32,u32), 16 for (u64,u64)); the key of `kind` sits at byte
+ * offset key_off inside each record. */
+size_t b200sort_records_temp_bytes(size_t n, size_t rec_bytes, int kind);
+int b200sort_records_device(void *d_recs, void *d_tmp, size_t tmp_bytes, size_t n,
+                            size_t rec_bytes, size_t key_off, int kind, void *stream);
+int b200sort_records_host(void *recs, size_t n, size_t rec_bytes, size_t key_off, int kind);
+
+/* ---- instrumentation (bench / tests; not on the reference's API) ---------- */
+
+/* Number of kernels the library has launched from this process so far
+ * (memset nodes not counted).  bench.py reports the delta as gpu_launches. */
+unsigned long long b200sort_launch_count(void);
+
+/* Kernel-tuning override for sweeps: variant index per key width (bytes).
+ * -1 restores the default.  Returns B200SORT_ERR_INVALID_ARG if unknown. */
+int b200sort_set_variant(int key_bytes, int variant);
+
+/* Per-phase timing of one device sort, measured with CUDA events on `stream`
+ * (synchronises!).  out_ms[0] = K1 histogram, out_ms[1] = K2 scan,
+ * out_ms[2 + p] = digit pass p (0 if skipped), out_ms[2 + D] = copy-back,
+ * out_ms[3 + D] = total.  out_len must be >= D + 4. */
+int b200sort_keys_device_timed(void *d_keys, void *d_tmp, size_t tmp_bytes, size_t n,
+                               int kind, void *stream, unsigned flags,
+                               float *out_ms, int out_len);
+
+/* ---- synthetic inputs and on-device verification (K5 / K6) ---------------- */
+
+/* distribution families of src/distr.rs, restated as counter-based generators
+ * (value = f(seed, index)), identical on CPU (radix_sort_b200/distr.py). */
+typedef enum b200sort_distr {
+    B200SORT_DISTR_UNIFORM = 0,    /* Standard / KeyUniform     distr.rs:40-52  */
+    B200SORT_DISTR_GEOMETRIC = 1,  /* MyExp(lambda)=Geometric   distr.rs:4-38   */
+    B200SORT_DISTR_ZIPF = 2,       /* ZipfU32/ZipfU64(s)        distr.rs:54-76,108-130 */
+    B200SORT_DISTR_STEP = 3,       /* StepUniformU32/U64(m)     distr.rs:78-106,132-160 */
+    B200SORT_DISTR_ASCENDING = 4,  /* presorted (builder's; not in distr.rs) */
+    B200SORT_DISTR_DESCENDING = 5, /* presorted, reversed (builder's) */
+    B200SORT_DISTR_FLOAT_TEST = 6  /* Uniform[-1,1) + specials  tests.rs:135-143 */
+} b200sort_distr;
+
+/* Fill d_keys[0..n) with keys index_base .. index_base+n of the stream
+ * (seed, distr, param).  param: lambda (GEOMETRIC), s (ZIPF), m (STEP). */
+int b200sort_generate(void *d_keys, size_t n, int kind, int distr, double param,
+                      uint64_t seed, uint64_t index_base, void *stream);
+
+/* Order-independent multiset fingerprint of d_keys[0..n):
+ * out[0] = n, out[1] = sum mix64(key) mod 2^64, out[2] = xor mix64(key),
+ * out[3] = sum key-low-64 mod 2^64.  d_out: 4 x uint64 on the device. */
+int b200sort_fingerprint(const void *d_keys, size_t n, int kind, uint64_t *d_out,
+                         void *stream);
+
+/* Count adjacent pairs that are out of order under get_digit's order:
+ * *d_out (uint64 on the device) = #{i : key[i] > key[i+1]}. 0 <=> sorted. */
+int b200sort_count_unsorted(const void *d_keys, size_t n, int kind, uint64_t *d_out,
+                            void *stream);
+
+/* ---- multi-GPU building blocks (one process per GPU; the exchange itself is
+ * NCCL all-to-all driven from the host side, radix_sort_b200/mgpu.py) -------- */
+
+/* K7: stable partition of d_in[0..n) by destination rank.  A key goes to rank
+ * r = #{j : splitters[j] <= key}, 0 <= r <= nsplit (nsplit <= 15), compared in
+ * get_digit's order,
+ * where `splitters` are nsplit ascending keys of `kind` in HOST memory, given
+ * as raw key bit patterns.  Writes the keys grouped by destination to d_out
+ * and the per-destination counts (nsplit + 1 uint64) to d_counts.
+ * Workspace: b200sort_temp_bytes(n, kind). */
+int b200sort_partition_device(const void *d_in, void *d_out, void *d_tmp, size_t tmp_bytes,
+                              size_t n, int kind, const void *splitters, int nsplit,
+                              uint64_t *d_counts, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SORT_H */

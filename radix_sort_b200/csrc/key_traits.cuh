@@ -1,0 +1,194 @@
+// key_traits.cuh -- the device-side key model.
+//
+// Replaces RadixDigits::get_digit (reference src/radix_sort/radix_digits.rs).
+// The reference re-applies the order transform on every get_digit call
+// (radix_digits.rs:59,110-112); here a key is mapped ONCE into its
+// order-preserving unsigned image ("ordered" key) by the first executed pass,
+// stays in that form between passes, and is mapped back by the last executed
+// pass, so the inner loops only extract bytes.
+//
+//   unsigned  (radix_digits.rs:7-53)    ordered = x
+//   signed    (radix_digits.rs:55-101)  ordered = x ^ MIN
+//   f32/f64   (radix_digits.rs:103-124) ordered = b ^ ((b >> N-1) | MIN)   (arithmetic >>)
+//                                       inverse: t ^ (((t >> N-1) - 1) | MIN) (logical >>)
+#pragma once
+#include <stdint.h>
+
+namespace b200 {
+
+enum { XF_NONE = 0, XF_SIGNED = 1, XF_FLOAT = 2 };
+
+struct alignas(16) u128 {
+    unsigned long long lo, hi;
+};
+
+template <int BYTES> struct UIntOf;
+template <> struct UIntOf<1> { using type = uint8_t; };
+template <> struct UIntOf<2> { using type = uint16_t; };
+template <> struct UIntOf<4> { using type = uint32_t; };
+template <> struct UIntOf<8> { using type = unsigned long long; };
+template <> struct UIntOf<16> { using type = u128; };
+
+// ---- scalar keys (1..8 bytes) -------------------------------------------------
+template <typename U, int XF>
+__host__ __device__ __forceinline__ U to_ordered(U k) {
+    constexpr int BITS = (int)sizeof(U) * 8;
+    constexpr U SIGN = (U)((U)1 << (BITS - 1));
+    if (XF == XF_SIGNED) return (U)(k ^ SIGN);
+    if (XF == XF_FLOAT) {
+        U m = (k & SIGN) ? (U)~(U)0 : SIGN;
+        return (U)(k ^ m);
+    }
+    return k;
+}
+template <typename U, int XF>
+__host__ __device__ __forceinline__ U from_ordered(U t) {
+    constexpr int BITS = (int)sizeof(U) * 8;
+    constexpr U SIGN = (U)((U)1 << (BITS - 1));
+    if (XF == XF_SIGNED) return (U)(t ^ SIGN);
+    if (XF == XF_FLOAT) {
+        U m = (t & SIGN) ? SIGN : (U)~(U)0;
+        return (U)(t ^ m);
+    }
+    return t;
+}
+template <typename U>
+__host__ __device__ __forceinline__ unsigned digit_of(U k, int pass) {
+    return (unsigned)(k >> (8 * pass)) & 0xFFu;
+}
+template <typename U>
+__host__ __device__ __forceinline__ bool ordered_less(U a, U b) { return a < b; }
+template <typename U>
+__host__ __device__ __forceinline__ unsigned long long low64(U k) { return (unsigned long long)k; }
+
+// ---- 128-bit keys (radix_digits.rs:39-45, 87-93) ------------------------------
+template <>
+__host__ __device__ __forceinline__ u128 to_ordered<u128, XF_NONE>(u128 k) { return k; }
+template <>
+__host__ __device__ __forceinline__ u128 to_ordered<u128, XF_SIGNED>(u128 k) {
+    k.hi ^= 0x8000000000000000ull;
+    return k;
+}
+template <>
+__host__ __device__ __forceinline__ u128 from_ordered<u128, XF_NONE>(u128 k) { return k; }
+template <>
+__host__ __device__ __forceinline__ u128 from_ordered<u128, XF_SIGNED>(u128 k) {
+    k.hi ^= 0x8000000000000000ull;
+    return k;
+}
+template <>
+__host__ __device__ __forceinline__ unsigned digit_of<u128>(u128 k, int pass) {
+    unsigned long long w = pass < 8 ? k.lo : k.hi;
+    return (unsigned)(w >> (8 * (pass & 7))) & 0xFFu;
+}
+template <>
+__host__ __device__ __forceinline__ bool ordered_less<u128>(u128 a, u128 b) {
+    return a.hi < b.hi || (a.hi == b.hi && a.lo < b.lo);
+}
+template <>
+__host__ __device__ __forceinline__ unsigned long long low64<u128>(u128 k) { return k.lo; }
+
+// splitmix64 finaliser: the mixing function of the counter-based generators
+// and of the multiset fingerprint.
+__host__ __device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+// Key-only element traits: the element moved by the passes IS the key.
+template <typename U, int XF_>
+struct KeyTraits {
+    using elem_t = U;
+    using key_t = U;
+    static constexpr int XF = XF_;
+    static constexpr int KEY_BYTES = (int)sizeof(U);
+    static constexpr int DIGITS = (int)sizeof(U);  // NUMBER_OF_DIGITS, radix_digits.rs:8..117
+    struct Params {};
+    __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params&) { return to_ordered<U, XF_>(e); }
+    __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params&) { return from_ordered<U, XF_>(e); }
+    __device__ __forceinline__ static unsigned digit(elem_t e, int pass, const Params&) { return digit_of<U>(e, pass); }
+};
+
+// Partition traits (multi-GPU MSD step): one "pass" whose digit is the
+// destination rank of the key, r = #{j : splitter[j] <= ordered(key)}.  Keys are
+// moved raw; splitters are held in the ordered domain.
+constexpr int MAX_SPLITTERS = 15;
+template <typename U, int XF_>
+struct PartitionTraits {
+    using elem_t = U;
+    using key_t = U;
+    static constexpr int XF = XF_;
+    static constexpr int KEY_BYTES = (int)sizeof(U);
+    static constexpr int DIGITS = 1;
+    struct Params {
+        U spl[MAX_SPLITTERS];
+        int nsplit;
+    };
+    __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params&) { return e; }
+    __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params&) { return e; }
+    __device__ __forceinline__ static unsigned digit(elem_t e, int, const Params& p) {
+        const U k = to_ordered<U, XF_>(e);
+        unsigned r = 0;
+#pragma unroll
+        for (int j = 0; j < MAX_SPLITTERS; ++j)
+            if (j < p.nsplit && !ordered_less<U>(k, p.spl[j])) ++r;
+        return r;
+    }
+};
+
+// Record traits: `(K, V)` tuples moved whole, key = one field of the record
+// (radix_digits.rs:126-136).  R = unsigned type as wide as the record (8 or 16
+// bytes), K = unsigned type of the key, key_shift = 8 * byte offset of the key.
+template <typename R, typename K, int XF_> struct RecordTraits;
+
+template <typename K, int XF_>
+struct RecordTraits<unsigned long long, K, XF_> {  // 8-byte record, 4-byte key
+    using elem_t = unsigned long long;
+    using key_t = K;
+    static constexpr int XF = XF_;
+    static constexpr int KEY_BYTES = (int)sizeof(K);
+    static constexpr int DIGITS = (int)sizeof(K);
+    struct Params { int key_shift; };
+    __device__ __forceinline__ static K key(elem_t e, const Params& p) { return (K)(e >> p.key_shift); }
+    __device__ __forceinline__ static elem_t with_key(elem_t e, K k, const Params& p) {
+        const elem_t mask = (elem_t)(K)~(K)0 << p.key_shift;
+        return (e & ~mask) | ((elem_t)k << p.key_shift);
+    }
+    __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params& p) {
+        return with_key(e, to_ordered<K, XF_>(key(e, p)), p);
+    }
+    __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params& p) {
+        return with_key(e, from_ordered<K, XF_>(key(e, p)), p);
+    }
+    __device__ __forceinline__ static unsigned digit(elem_t e, int pass, const Params& p) {
+        return (unsigned)(e >> (p.key_shift + 8 * pass)) & 0xFFu;
+    }
+};
+
+template <int XF_>
+struct RecordTraits<u128, unsigned long long, XF_> {  // 16-byte record, 8-byte key
+    using elem_t = u128;
+    using key_t = unsigned long long;
+    static constexpr int XF = XF_;
+    static constexpr int KEY_BYTES = 8;
+    static constexpr int DIGITS = 8;
+    struct Params { int key_shift; };  // 0 -> key in .lo, 64 -> key in .hi
+    __device__ __forceinline__ static key_t key(elem_t e, const Params& p) { return p.key_shift ? e.hi : e.lo; }
+    __device__ __forceinline__ static elem_t with_key(elem_t e, key_t k, const Params& p) {
+        if (p.key_shift) e.hi = k; else e.lo = k;
+        return e;
+    }
+    __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params& p) {
+        return with_key(e, to_ordered<key_t, XF_>(key(e, p)), p);
+    }
+    __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params& p) {
+        return with_key(e, from_ordered<key_t, XF_>(key(e, p)), p);
+    }
+    __device__ __forceinline__ static unsigned digit(elem_t e, int pass, const Params& p) {
+        return (unsigned)(key(e, p) >> (8 * pass)) & 0xFFu;
+    }
+};
+
+}  // namespace b200

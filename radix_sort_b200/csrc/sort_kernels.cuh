@@ -1,0 +1,385 @@
+// sort_kernels.cuh -- the sm_100a kernels of the LSD radix sort.
+//
+//   K1 hist_all_digits_kernel  one read of the keys -> all D x 256 histograms
+//                              (replaces phase A, reference mod.rs:90-109; the
+//                              all-digits-up-front idea is the reference's own
+//                              radix_sort1, mod.rs:217-239)
+//   K2 scan_plan_kernel        exclusive scan of every histogram -> bucket bases,
+//                              plus the pass plan (replaces phase B, mod.rs:110-120)
+//   K3 onesweep_pass_kernel    one digit pass: stage tile -> rank -> decoupled
+//                              look-back -> coalesced write-out (replaces phase C,
+//                              the 96-element buffered scatter, mod.rs:121-168)
+//   K4 = the key transform, fused into K1 and into the first/last executed K3
+//   copy_back_kernel           odd number of executed passes (mod.rs:170-174)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "key_traits.cuh"
+
+namespace b200 {
+
+constexpr int RADIX = 256;          // 8-bit digits, radix_digits.rs:4 (get_digit -> u8)
+constexpr int MAX_DIGITS = 16;      // u128
+constexpr unsigned FULL_MASK = 0xFFFFFFFFu;
+
+// Look-back status word: {flag:2, value:30}.  A portion holds < 2^30 keys so an
+// inclusive prefix always fits.
+constexpr uint32_t LB_FLAG_PARTIAL = 1u << 30;
+constexpr uint32_t LB_FLAG_INCLUSIVE = 1u << 31;
+constexpr uint32_t LB_VALUE_MASK = (1u << 30) - 1u;
+
+struct PassPlan {
+    uint32_t skip;        // digit is constant over all keys: pass is the identity
+    uint32_t src_is_tmp;  // ping-pong side this pass reads (mod.rs:85-89)
+    uint32_t xf_in;       // first executed pass: map raw keys -> ordered keys on load
+    uint32_t xf_out;      // last executed pass: map ordered keys -> raw keys on store
+};
+struct Plan {
+    PassPlan pass[MAX_DIGITS];
+    uint32_t result_in_tmp;  // odd number of executed passes
+    uint32_t n_exec;
+};
+
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// read-only element load (LDG.E.*.CONSTANT); 128-bit elements go as one LDG.128
+template <typename E>
+__device__ __forceinline__ E ld_elem(const E* p) { return __ldg(p); }
+template <>
+__device__ __forceinline__ u128 ld_elem<u128>(const u128* p) {
+    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(p));
+    u128 r;
+    r.lo = v.x;
+    r.hi = v.y;
+    return r;
+}
+
+// ---------------------------------------------------------------------------
+// K1: all-digit histogram.  16-byte coalesced loads (LDG.128), four in flight
+// per thread; one privatised shared-memory histogram set per CTA; a digit that
+// is identical across the converged warp (constant high bytes, few-unique
+// inputs) costs one shared atomic per warp instead of 32 same-address ones.
+// ---------------------------------------------------------------------------
+template <typename Tr, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+hist_all_digits_kernel(const typename Tr::elem_t* __restrict__ in, size_t n,
+                       unsigned long long* __restrict__ hist, typename Tr::Params prm) {
+    using E = typename Tr::elem_t;
+    constexpr int D = Tr::DIGITS;
+    constexpr int VEC = 16 / (int)sizeof(E);
+    __shared__ uint32_t sh[D * RADIX];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < D * RADIX; i += THREADS) sh[i] = 0;
+    __syncthreads();
+
+    auto count = [&](E raw) {
+        const E e = Tr::xform_in(raw, prm);
+        const unsigned active = __activemask();
+        const int leader = __ffs(active) - 1;
+        const unsigned lane = tid & 31;
+#pragma unroll
+        for (int p = 0; p < D; ++p) {
+            const unsigned d = Tr::digit(e, p, prm);
+            const unsigned d0 = __shfl_sync(active, d, leader);
+            if (__all_sync(active, d == d0)) {
+                if ((int)lane == leader) atomicAdd(&sh[p * RADIX + d0], (uint32_t)__popc(active));
+            } else {
+                atomicAdd(&sh[p * RADIX + d], 1u);
+            }
+        }
+    };
+    auto count_vec = [&](uint4 v) {
+        union { uint4 v; E e[VEC]; } u;
+        u.v = v;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) count(u.e[j]);
+    };
+
+    // peel to 16-byte alignment, then whole vectors, then the tail
+    const uintptr_t addr = (uintptr_t)in;
+    size_t head = ((16 - (addr & 15)) & 15) / sizeof(E);
+    if (head > n) head = n;
+    const uint4* vec = reinterpret_cast<const uint4*>(in + head);
+    const size_t nvec = (n - head) / VEC;
+    const size_t tail = head + nvec * VEC;
+
+    const size_t stride = (size_t)gridDim.x * THREADS;
+    size_t i = (size_t)blockIdx.x * THREADS + tid;
+    for (; i + 3 * stride < nvec; i += 4 * stride) {
+        const uint4 a = __ldg(vec + i);
+        const uint4 b = __ldg(vec + i + stride);
+        const uint4 c = __ldg(vec + i + 2 * stride);
+        const uint4 d = __ldg(vec + i + 3 * stride);
+        count_vec(a); count_vec(b); count_vec(c); count_vec(d);
+    }
+    for (; i < nvec; i += stride) count_vec(__ldg(vec + i));
+    if (blockIdx.x == 0) {
+        for (size_t j = tid; j < head; j += THREADS) count(ld_elem(in + j));
+        for (size_t j = tail + tid; j < n; j += THREADS) count(ld_elem(in + j));
+    }
+    __syncthreads();
+    for (int k = tid; k < D * RADIX; k += THREADS) {
+        const uint32_t c = sh[k];
+        if (c) atomicAdd(&hist[k], (unsigned long long)c);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K2: one CTA of 256 threads.  For every digit: exclusive scan of its 256-bin
+// histogram -> global bucket bases of portion 0 (64-bit); detection of constant
+// digits; then thread 0 lays out the pass plan (ping-pong side, where the key
+// transform is applied, where the result ends up).
+// bins layout: [digit][portion][256].
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(RADIX)
+scan_plan_kernel(const unsigned long long* __restrict__ hist, unsigned long long* __restrict__ bins,
+                 Plan* __restrict__ plan, unsigned long long n, int digits, int portions, int no_skip) {
+    __shared__ unsigned long long warp_tot[RADIX / 32];
+    __shared__ uint32_t s_skip[MAX_DIGITS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int p = 0; p < digits; ++p) {
+        const unsigned long long c = hist[p * RADIX + tid];
+        unsigned long long x = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long y = __shfl_up_sync(FULL_MASK, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_tot[warp] = x;
+        const int is_const = __syncthreads_or(c == n);
+        unsigned long long base = 0;
+        for (int w = 0; w < warp; ++w) base += warp_tot[w];
+        bins[((size_t)p * portions) * RADIX + tid] = base + x - c;
+        if (tid == 0) s_skip[p] = (is_const && !no_skip) ? 1u : 0u;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        int first = -1, last = -1, n_exec = 0;
+        for (int p = 0; p < digits; ++p)
+            if (!s_skip[p]) { if (first < 0) first = p; last = p; }
+        for (int p = 0; p < MAX_DIGITS; ++p) {
+            PassPlan pp;
+            pp.skip = (p < digits) ? s_skip[p] : 1u;
+            pp.src_is_tmp = (uint32_t)(n_exec & 1);
+            pp.xf_in = (p == first);
+            pp.xf_out = (p == last);
+            plan->pass[p] = pp;
+            if (!pp.skip) ++n_exec;
+        }
+        plan->n_exec = (uint32_t)n_exec;
+        plan->result_in_tmp = (uint32_t)(n_exec & 1);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K3: one digit pass over one portion (< 2^30 elements), onesweep style.
+// ---------------------------------------------------------------------------
+template <typename Tr>
+struct PassArgs {
+    typename Tr::elem_t* keys;           // caller's buffer
+    typename Tr::elem_t* tmp;            // ping-pong buffer (mod.rs:71-83)
+    const Plan* plan;
+    int pass;                            // digit index (mod.rs:84)
+    unsigned long long portion_off;      // first element of this portion
+    uint32_t portion_n;                  // elements in this portion
+    uint32_t num_tiles;
+    const unsigned long long* bins_in;   // [256] global base of each bucket for this portion
+    unsigned long long* bins_out;        // [256] base for the next portion (or null)
+    uint32_t* lookback;                  // [num_tiles][256] status words, zeroed
+    uint32_t* ticket;                    // tile-id dispenser, zeroed
+    typename Tr::Params prm;
+};
+
+template <typename Tr, int THREADS, int ITEMS>
+struct PassSmem {
+    static constexpr int WARPS = THREADS / 32;
+    static constexpr int TILE = THREADS * ITEMS;
+    static constexpr size_t HIST_BYTES = (size_t)WARPS * RADIX * sizeof(uint32_t);
+    static constexpr size_t TILE_BYTES = (size_t)TILE * sizeof(typename Tr::elem_t);
+    static constexpr size_t GOFF_BYTES = (size_t)RADIX * sizeof(long long);
+    static constexpr size_t EXCL_BYTES = (size_t)RADIX * sizeof(uint32_t);
+    static constexpr size_t TOTAL = HIST_BYTES + TILE_BYTES + GOFF_BYTES + EXCL_BYTES + 64;
+};
+
+template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+onesweep_pass_kernel(const PassArgs<Tr> a) {
+    using E = typename Tr::elem_t;
+    using SM = PassSmem<Tr, THREADS, ITEMS>;
+    constexpr int WARPS = SM::WARPS;
+    constexpr int TILE = SM::TILE;
+    static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit needed");
+
+    const PassPlan pp = a.plan->pass[a.pass];
+    if (pp.skip) return;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    E* tile_s = reinterpret_cast<E*>(smem_raw);
+    uint32_t* warp_hist = reinterpret_cast<uint32_t*>(smem_raw + SM::TILE_BYTES);
+    long long* goff = reinterpret_cast<long long*>(smem_raw + SM::TILE_BYTES + SM::HIST_BYTES);
+    uint32_t* s_excl = reinterpret_cast<uint32_t*>(smem_raw + SM::TILE_BYTES + SM::HIST_BYTES + SM::GOFF_BYTES);
+    uint32_t* s_misc = s_excl + RADIX;  // [0] ticket, [1..] warp totals of the digit scan
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lane_lt = (1u << lane) - 1u;
+    const int pass = a.pass;
+
+    const E* __restrict__ src = (pp.src_is_tmp ? a.tmp : a.keys) + a.portion_off;
+    E* __restrict__ dst = pp.src_is_tmp ? a.keys : a.tmp;
+
+    // tile id from a ticket, not blockIdx: every predecessor a tile may wait on
+    // in the look-back has already started, whatever order CTAs are dispatched in
+    if (tid == 0) s_misc[0] = atomicAdd(a.ticket, 1u);
+#pragma unroll
+    for (int i = tid; i < WARPS * RADIX; i += THREADS) warp_hist[i] = 0;
+    __syncthreads();
+    const uint32_t tile = s_misc[0];
+    const uint32_t tile_base = tile * (uint32_t)TILE;
+    const uint32_t tile_n = min((uint32_t)TILE, a.portion_n - tile_base);
+    const bool full = (tile_n == (uint32_t)TILE);
+
+    // ---- stage: warp-striped load (item i of lane l = element i*32+l of the
+    // warp's contiguous segment), so rank order == memory order
+    E e[ITEMS];
+    const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
+    const E* p = src + tile_base + wbase;
+    if (full) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) e[i] = ld_elem(p + i * 32);
+    } else {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+            if (wbase + i * 32 < tile_n) e[i] = ld_elem(p + i * 32);
+    }
+    if (pp.xf_in) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) e[i] = Tr::xform_in(e[i], a.prm);
+    }
+
+    // ---- early counts: per-warp digit histograms by shared atomics
+    uint32_t* my_hist = warp_hist + warp * RADIX;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i)
+        if (full || wbase + i * 32 < tile_n) atomicAdd(&my_hist[Tr::digit(e[i], pass, a.prm)], 1u);
+    __syncthreads();
+
+    // ---- thread d owns digit d: column-reduce the warp histograms into
+    // exclusive-over-warps prefixes, publish the tile's count, scan over digits
+    uint32_t count = 0;
+    uint32_t* lb = a.lookback + (size_t)tile * RADIX;
+    if (tid < RADIX) {
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; ++w) {
+            const uint32_t t = warp_hist[w * RADIX + tid];
+            warp_hist[w * RADIX + tid] = run;
+            run += t;
+        }
+        count = run;
+        st_relaxed_u32(lb + tid, (tile == 0 ? LB_FLAG_INCLUSIVE : LB_FLAG_PARTIAL) | count);
+    }
+    uint32_t incl = count;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(FULL_MASK, incl, o);
+        if (lane >= o) incl += y;
+    }
+    if (lane == 31 && warp < RADIX / 32) s_misc[1 + warp] = incl;
+    __syncthreads();
+    if (tid < RADIX) {
+        uint32_t base = 0;
+#pragma unroll
+        for (int w = 0; w < RADIX / 32; ++w) base += (w < warp) ? s_misc[1 + w] : 0u;
+        s_excl[tid] = base + incl - count;  // keys of the tile with a smaller digit
+    }
+    __syncthreads();
+
+    // ---- rank: __match_any_sync groups the lanes holding the same digit; the
+    // lowest lane of a group bumps the warp's running counter for the group
+    uint32_t rank[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        const unsigned d = Tr::digit(e[i], pass, a.prm);
+        unsigned m = __match_any_sync(FULL_MASK, d);
+        if (!full) m &= __ballot_sync(FULL_MASK, wbase + i * 32 < tile_n);
+        const int leader = __ffs(m) - 1;
+        uint32_t old = 0;
+        if (lane == leader) {
+            old = my_hist[d];
+            my_hist[d] = old + __popc(m);
+        }
+        old = __shfl_sync(FULL_MASK, old, leader & 31);
+        rank[i] = old + __popc(m & lane_lt) + s_excl[d];
+        __syncwarp();
+    }
+
+    // ---- decoupled look-back (digit threads): sum the counts of preceding
+    // tiles until one that already knows its inclusive prefix
+    if (tid < RADIX) {
+        unsigned long long excl_tiles = 0;
+        if (tile > 0) {
+            uint32_t sum = 0;
+            const uint32_t* q = lb + tid;
+            for (;;) {
+                q -= RADIX;
+                uint32_t v;
+                do { v = ld_relaxed_u32(q); } while ((v & (LB_FLAG_PARTIAL | LB_FLAG_INCLUSIVE)) == 0);
+                sum += v & LB_VALUE_MASK;
+                if (v & LB_FLAG_INCLUSIVE) break;
+            }
+            st_relaxed_u32(lb + tid, LB_FLAG_INCLUSIVE | (sum + count));
+            excl_tiles = sum;
+        }
+        const unsigned long long gbase = a.bins_in[tid] + excl_tiles;
+        goff[tid] = (long long)gbase - (long long)s_excl[tid];
+        if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[tid] = gbase + count;
+    }
+
+    // ---- tile-local sort in shared memory, then coalesced run write-out
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i)
+        if (full || wbase + i * 32 < tile_n) tile_s[rank[i]] = e[i];
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const uint32_t idx = (uint32_t)j * THREADS + tid;
+        if (full || idx < tile_n) {
+            E v = tile_s[idx];
+            const unsigned d = Tr::digit(v, pass, a.prm);
+            if (pp.xf_out) v = Tr::xform_out(v, a.prm);
+            dst[goff[d] + (long long)idx] = v;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Odd number of executed passes: the result sits in tmp (mod.rs:170-174).
+// Exits at once when the plan says the result is already in the caller's buffer.
+// ---------------------------------------------------------------------------
+template <typename E>
+__global__ void __launch_bounds__(256)
+copy_back_kernel(E* __restrict__ keys, const E* __restrict__ tmp, size_t n, const Plan* __restrict__ plan) {
+    if (!plan->result_in_tmp) return;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if ((((uintptr_t)keys | (uintptr_t)tmp) & 15) == 0) {
+        constexpr size_t VEC = 16 / sizeof(E);
+        const size_t nvec = n / VEC;
+        const uint4* s = reinterpret_cast<const uint4*>(tmp);
+        uint4* d = reinterpret_cast<uint4*>(keys);
+        for (size_t i = t0; i < nvec; i += stride) d[i] = s[i];
+        for (size_t i = nvec * VEC + t0; i < n; i += stride) keys[i] = tmp[i];
+    } else {
+        for (size_t i = t0; i < n; i += stride) keys[i] = tmp[i];
+    }
+}
+
+}  // namespace b200

@@ -1,0 +1,405 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle and the
+independent numpy statement of the reference's test oracle, bit for bit.
+
+The first block restates the reference's 15 tests (src/radix_sort/tests.rs) one
+for one -- same sizes (1e6), same input families, same equality -- with fixed
+seeds instead of thread_rng().  The rest covers what the reference leaves
+untested (tests.rs has no n==0, tiny n, duplicates, presorted, negative NaN...).
+"""
+import ctypes
+import threading
+
+import numpy as np
+import pytest
+
+import radix_sort_b200 as rs
+from oracle import cpu_oracle
+from radix_sort_b200 import _ffi, distr, verify
+from tests import _ref
+
+pytestmark = pytest.mark.gpu
+
+N_REF = 1_000_000  # 1e6 as usize, tests.rs:27,36,45,...
+
+
+def _kind(name):
+    return rs.Kind[name.upper()]
+
+
+def _check_host(a, kind):
+    """sort a copy through b200sort_keys_host; compare with oracle and numpy."""
+    want_np = _ref.expected_sorted(a, kind)
+    want_or = a.copy()
+    cpu_oracle.sort0(want_or, kind)
+    assert _ref.same_bits(want_or, want_np), "oracle and numpy disagree"
+    got = a.copy()
+    rs.radix_sort(got, _kind(kind))
+    assert _ref.same_bits(got, want_or), f"{kind}: GPU result differs from the oracle"
+
+
+def _to_device(a, cuda):
+    import torch
+    return torch.from_numpy(a).to(cuda)
+
+
+def _check_device(a, kind, cuda, **kw):
+    import torch
+    want = a.copy()
+    cpu_oracle.sort0(want, kind)
+    t = _to_device(a, cuda)
+    rs.radix_sort(t, _kind(kind), **kw)
+    torch.cuda.synchronize()
+    got = t.cpu().numpy()
+    assert _ref.same_bits(got, want), f"{kind}: GPU device-path result differs from the oracle"
+
+
+# ---- the reference's 15 tests, restated (tests.rs:25-187) -------------------------
+
+@pytest.mark.parametrize("kind", ["u8", "u16", "u32", "u64", "u128", "u64"],
+                         ids=["radix_sort_u8", "radix_sort_u16", "radix_sort_u32", "radix_sort_u64",
+                              "radix_sort_u128", "radix_sort_usize"])
+def test_ref_unsigned(kind, cuda):  # tests.rs:25-77
+    _check_host(_ref.random_keys(kind, N_REF, seed=0xB200 + len(kind)), kind)
+
+
+@pytest.mark.parametrize("kind", ["i8", "i16", "i32", "i64", "i128", "i64"],
+                         ids=["radix_sort_i8", "radix_sort_i16", "radix_sort_i32", "radix_sort_i64",
+                              "radix_sort_i128", "radix_sort_isize"])
+def test_ref_signed(kind, cuda):  # tests.rs:79-131
+    _check_host(_ref.random_keys(kind, N_REF, seed=0x5200 + len(kind)), kind)
+
+
+@pytest.mark.parametrize("kind", ["f32", "f64"], ids=["radix_sort_f32", "radix_sort_f64"])
+def test_ref_floats(kind, cuda):  # tests.rs:133-173: Uniform(-1,1) + {0.0,-0.0,NAN,INF,-INF}
+    _check_host(_ref.float_test_keys(kind, N_REF, seed=77), kind)
+
+
+def test_ref_tuple(cuda):  # tests.rs:175-187: random (u32,u32), stable sort_by_key(|e| e.0)
+    rng = np.random.default_rng(1234)
+    recs = rng.integers(0, 2**32, size=(N_REF, 2), dtype=np.uint64).astype(np.uint32)
+    want = _ref.expected_sorted_records(recs, "u32")
+    want_or = recs.copy()
+    cpu_oracle.sort0(want_or, "pair_u32")
+    assert _ref.same_bits(want, want_or)
+    got = recs.copy()
+    rs.radix_sort_records(got, rs.Kind.U32, key_off=0)
+    assert _ref.same_bits(got, want)
+
+
+# ---- every kind, device-resident path, edge sizes ----------------------------------
+
+EDGE_SIZES = [1, 2, 31, 32, 33, 95, 96, 97, 255, 256, 257, 3071, 3072, 3073, 8191, 8192, 8193, 16385, 100_003]
+
+
+@pytest.mark.parametrize("kind", _ref.KINDS)
+def test_device_path_edge_sizes(kind, cuda):
+    for n in EDGE_SIZES:
+        _check_device(_ref.random_keys(kind, n, seed=n), kind, cuda)
+
+
+@pytest.mark.parametrize("kind", _ref.KINDS)
+def test_host_path_small_and_odd(kind, cuda):
+    for n in (1, 2, 97, 1_000_001):
+        _check_host(_ref.random_keys(kind, n, seed=n + 7), kind)
+
+
+@pytest.mark.parametrize("kind", ["u8", "u16", "u32", "u64", "i32", "i64", "f32", "f64", "u128"])
+def test_degenerate_inputs_skip_and_no_skip(kind, cuda):
+    import torch
+    n = 300_000
+    kb = _ref.KEY_BYTES[kind]
+    base = _ref.random_keys(kind, n, seed=1)
+    cases = {
+        "all_equal": np.repeat(base[:1], n, axis=0),
+        "two_values": base[np.arange(n) % 2],
+        "low_byte_only": None,
+    }
+    flat = base.view(np.uint8).reshape(n, kb).copy()
+    flat[:, 1:] = 0x5A if kb > 1 else flat[:, 1:]
+    cases["low_byte_only"] = flat.view(base.dtype).reshape(base.shape)
+    srt = base.copy(); cpu_oracle.sort0(srt, kind)
+    cases["ascending"] = srt
+    cases["descending"] = srt[::-1].copy()
+    for name, a in cases.items():
+        a = np.ascontiguousarray(a)
+        _check_device(a, kind, cuda)
+        _check_device(a, kind, cuda, flags=rs.FLAG_NO_SKIP)
+
+
+def test_known_answer_float_order(cuda):
+    # -NaN < -inf < ... < -0 < +0 < ... < +inf < +NaN, NaNs by payload
+    bits = np.array([0xFFC00000, 0xFF800001, 0xFF800000, 0xBF800000, 0x80000001, 0x80000000, 0x00000000,
+                     0x00000001, 0x3F800000, 0x7F800000, 0x7F800001, 0x7FC00000, 0x7FFFFFFF], dtype=np.uint32)
+    a = bits[::-1].copy().view(np.float32)
+    rs.radix_sort(a)
+    assert a.view(np.uint32).tolist() == bits.tolist()
+    b = np.array([0x7FFFFFFF, 0, 0x80000000, 0xFFFFFFFF, 1], dtype=np.uint32).view(np.int32)
+    rs.radix_sort(b)
+    assert b.tolist() == [-(2**31), -1, 0, 1, 2**31 - 1]
+
+
+def test_f64_specials_and_subnormals(cuda):
+    vals = np.array([np.inf, -0.0, 1.0, np.nan, 0.0, -np.inf, -1.0, -np.nan, 5e-324, -5e-324,
+                     1.7976931348623157e308, -1.7976931348623157e308] * 1000, dtype=np.float64)
+    _check_host(vals, "f64")
+
+
+# ---- distribution families of distr.rs, generated on the device (K5) ---------------
+
+@pytest.mark.parametrize("kind,dist,param", [
+    ("u32", distr.Distr.UNIFORM, 0), ("u64", distr.Distr.UNIFORM, 0), ("u128", distr.Distr.UNIFORM, 0),
+    ("u32", distr.Distr.GEOMETRIC, 2.0 ** -10), ("u64", distr.Distr.GEOMETRIC, 2.0 ** -10),
+    ("u32", distr.Distr.ZIPF, 0.75), ("u32", distr.Distr.ZIPF, 1.0), ("u32", distr.Distr.ZIPF, 1.5),
+    ("u64", distr.Distr.ZIPF, 1.0),
+    ("u32", distr.Distr.STEP, 1), ("u32", distr.Distr.STEP, 2), ("u32", distr.Distr.STEP, 16),
+    ("u32", distr.Distr.STEP, 256), ("u32", distr.Distr.STEP, 65536), ("u64", distr.Distr.STEP, 256),
+    ("u32", distr.Distr.ASCENDING, 2_000_003), ("u32", distr.Distr.DESCENDING, 2_000_003),
+    ("u64", distr.Distr.DESCENDING, 2_000_003),
+    ("f32", distr.Distr.FLOAT_TEST, 1000), ("f64", distr.Distr.FLOAT_TEST, 1000),
+    ("f32", distr.Distr.UNIFORM, 0), ("f64", distr.Distr.UNIFORM, 0),
+    ("i32", distr.Distr.UNIFORM, 0), ("i64", distr.Distr.UNIFORM, 0),
+])
+def test_distribution_families(kind, dist, param, cuda):
+    import torch
+    n = 2_000_003
+    t = distr.empty_keys(n, _kind(kind), cuda)
+    distr.generate(t, _kind(kind), dist, param, seed=0xB2000004)
+    torch.cuda.synchronize()
+    a = t.cpu().numpy()
+    if dist == distr.Distr.UNIFORM:  # the numpy mirror of the stream is bit-identical
+        assert _ref.same_bits(a, distr.uniform_host(n, _kind(kind), seed=0xB2000004))
+    if dist == distr.Distr.STEP:
+        assert len(np.unique(a)) == min(int(param), n)
+    want = a.copy()
+    cpu_oracle.sort0(want, kind)
+    fp_before = verify.fingerprint(t, _kind(kind))
+    rs.radix_sort(t, _kind(kind))
+    torch.cuda.synchronize()
+    assert _ref.same_bits(t.cpu().numpy(), want)
+    assert verify.count_unsorted(t, _kind(kind)) == 0
+    assert verify.fingerprint(t, _kind(kind)) == fp_before
+
+
+# ---- records: (K, V) tuples, stable (radix_digits.rs:126-136) ----------------------
+
+@pytest.mark.parametrize("key_kind,dt", [("u32", np.uint32), ("i32", np.int32), ("f32", np.float32),
+                                         ("u64", np.uint64), ("i64", np.int64), ("f64", np.float64)])
+@pytest.mark.parametrize("key_col", [0, 1])
+def test_records_stable_host_and_device(key_kind, dt, key_col, cuda):
+    import torch
+    rng = np.random.default_rng(99)
+    n = 500_003
+    kb = np.dtype(dt).itemsize
+    udt = np.uint32 if kb == 4 else np.uint64
+    recs = np.empty((n, 2), dtype=udt)
+    # few distinct keys -> long runs of equal keys -> stability is observable
+    keys = rng.integers(0, 2**(8 * kb), size=n, dtype=np.uint64).astype(udt)
+    keys[rng.random(n) < 0.9] &= udt(0xFF0000FF if kb == 4 else 0xFF000000000000FF)
+    recs[:, key_col] = keys
+    recs[:, 1 - key_col] = np.arange(n, dtype=udt)  # payload = original position
+    typed = recs.view(dt)
+    want = _ref.expected_sorted_records(typed, key_kind, key_col)
+    got = typed.copy()
+    rs.radix_sort_records(got, _kind(key_kind), key_off=key_col * kb)
+    assert _ref.same_bits(got, want)
+    t = torch.from_numpy(recs.view(np.int32 if kb == 4 else np.int64)).to(cuda)
+    rs.radix_sort_records(t, _kind(key_kind), key_off=key_col * kb)
+    torch.cuda.synchronize()
+    assert _ref.same_bits(t.cpu().numpy(), want)
+
+
+def test_demo_shapes_pairs_payload_zero(cuda):
+    # main.rs:101-126 + distr.rs:42-52: KeyUniform pairs (random key, payload 0)
+    for udt, kind, oracle_kind in ((np.uint32, rs.Kind.U32, "pair_u32"), (np.uint64, rs.Kind.U64, "pair_u64")):
+        n = 1_000_000
+        recs = np.zeros((n, 2), dtype=udt)
+        recs[:, 0] = distr.uniform_host(n, kind, seed=5)
+        want = recs.copy()
+        cpu_oracle.sort0(want, oracle_kind)
+        rs.radix_sort_records(recs, kind)
+        assert _ref.same_bits(recs, want)
+
+
+# ---- kernel variants, alignment, re-entrancy, graphs --------------------------------
+
+@pytest.mark.parametrize("kind,kb,nvar", [("u8", 1, 2), ("u16", 2, 2), ("u32", 4, 6), ("u64", 8, 6), ("u128", 16, 3)])
+def test_every_kernel_variant(kind, kb, nvar, cuda):
+    a = _ref.random_keys(kind, 777_777, seed=3)
+    try:
+        for v in range(nvar):
+            rs.set_variant(kb, v)
+            _check_device(a, kind, cuda)
+    finally:
+        rs.set_variant(kb, -1)
+
+
+@pytest.mark.parametrize("kind", ["u8", "u16", "u32", "u64"])
+def test_unaligned_device_slice(kind, cuda):
+    import torch
+    a = _ref.random_keys(kind, 200_003, seed=8)
+    t = _to_device(a, cuda)
+    for off in (1, 3):
+        sub = t[off:]
+        want = a[off:].copy()
+        cpu_oracle.sort0(want, kind)
+        rs.radix_sort(sub, _kind(kind))
+        torch.cuda.synchronize()
+        assert _ref.same_bits(sub.cpu().numpy(), want)
+        assert _ref.same_bits(t[:off].cpu().numpy(), a[:off])  # prefix untouched
+        t = _to_device(a, cuda)
+
+
+def test_concurrent_host_calls(cuda):
+    # libtest runs the reference's tests on parallel threads
+    kinds = ["u32", "u64", "i32", "f64", "u16", "u128", "i8", "f32"]
+    inputs = [_ref.random_keys(k, 400_000 + 1000 * i, seed=i) for i, k in enumerate(kinds)]
+    outs = [a.copy() for a in inputs]
+    errs = []
+
+    def work(i):
+        try:
+            for _ in range(3):
+                outs[i][...] = inputs[i]
+                rs.radix_sort(outs[i], _kind(kinds[i]))
+        except Exception as exc:  # noqa: BLE001
+            errs.append(exc)
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(len(kinds))]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
+    for k, a, got in zip(kinds, inputs, outs):
+        want = a.copy()
+        cpu_oracle.sort0(want, k)
+        assert _ref.same_bits(got, want)
+
+
+def test_cuda_graph_capture_of_device_sort(cuda):
+    import torch
+    n = 1_000_000
+    a = _ref.random_keys("u32", n, seed=21)
+    want = a.copy()
+    cpu_oracle.sort0(want, "u32")
+    src = _to_device(a, cuda)
+    keys = torch.empty_like(src)
+    ws = torch.empty(rs.temp_bytes(n, rs.Kind.U32), dtype=torch.uint8, device=cuda)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        keys.copy_(src)
+        rs.radix_sort(keys, workspace=ws)  # warm: sets function attributes outside capture
+    s.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=s):
+        keys.copy_(src)
+        rs.radix_sort(keys, workspace=ws)
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    assert _ref.same_bits(keys.cpu().numpy(), want)
+
+
+def test_workspace_too_small_is_rejected(cuda):
+    import torch
+    t = torch.zeros(1000, dtype=torch.int32, device=cuda)
+    with pytest.raises(rs.B200SortError) as e:
+        rs.radix_sort(t, workspace=torch.empty(256, dtype=torch.uint8, device=cuda))
+    assert e.value.code == 1
+
+
+def test_copyonly_aliases_and_counting_sort(cuda):
+    a = _ref.random_keys("u8", 100_000, seed=4)
+    want = np.sort(a)
+    b = a.copy(); rs.counting_sort(b)
+    assert _ref.same_bits(b, want)
+    for fn in (rs.radix_sort0, rs.radix_sort1, rs.radix_sort2, rs.radix_sort3, rs.radix_sort4, rs.radix_sort5):
+        c = a.copy(); fn(c)
+        assert _ref.same_bits(c, want)
+
+
+# ---- multi-GPU building block: K7 partition ------------------------------------------
+
+@pytest.mark.parametrize("kind", ["u32", "u64", "i64", "f32"])
+def test_partition_by_splitters(kind, cuda):
+    import torch
+    n = 1_500_001
+    a = _ref.random_keys(kind, n, seed=31)
+    srt = _ref.expected_sorted(a, kind)
+    nsplit = 7
+    spl = np.ascontiguousarray(srt[[n * (j + 1) // (nsplit + 1) for j in range(nsplit)]])
+    # destination of every key in get_digit's order: its rank among the splitters
+    if kind in ("f32", "f64"):
+        keyv = _ref.total_cmp_key(a.view(np.int32 if kind == "f32" else np.int64))
+        splv = _ref.total_cmp_key(spl.view(np.int32 if kind == "f32" else np.int64))
+    else:
+        keyv, splv = a, spl
+    dest = np.searchsorted(splv, keyv, side="right")  # #{j : spl[j] <= key}
+    want = np.concatenate([a[dest == r] for r in range(nsplit + 1)])  # stable by destination
+    want_counts = np.bincount(dest, minlength=nsplit + 1)
+
+    L = _ffi.lib()
+    d_in = _to_device(a, cuda)
+    d_out = torch.empty_like(d_in)
+    ws = torch.empty(rs.temp_bytes(n, _kind(kind)), dtype=torch.uint8, device=cuda)
+    counts = torch.zeros(nsplit + 1, dtype=torch.int64, device=cuda)
+    st = torch.cuda.current_stream().cuda_stream
+    rc = L.b200sort_partition_device(d_in.data_ptr(), d_out.data_ptr(), ws.data_ptr(), ws.numel(), n,
+                                     int(_kind(kind)), spl.ctypes.data, nsplit, counts.data_ptr(),
+                                     ctypes.c_void_p(st))
+    assert rc == 0, L.b200sort_last_error()
+    torch.cuda.synchronize()
+    assert counts.cpu().numpy().tolist() == want_counts.tolist()
+    assert _ref.same_bits(d_out.cpu().numpy(), want)
+    assert _ref.same_bits(d_in.cpu().numpy(), a)  # input untouched
+
+
+# ---- full-size runs: size-independent properties (sorted + same multiset) ------------
+
+def _property_run(kind, n, dist, param, cuda, seed=0xB2000002):
+    import torch
+    k = _kind(kind)
+    t = distr.empty_keys(n, k, cuda)
+    distr.generate(t, k, dist, param, seed=seed)
+    fp = verify.fingerprint(t, k)
+    assert fp[0] == n
+    ws = torch.empty(rs.temp_bytes(n, k), dtype=torch.uint8, device=cuda)
+    rs.radix_sort(t, k, workspace=ws)
+    torch.cuda.synchronize()
+    assert verify.count_unsorted(t, k) == 0, "not sorted"
+    assert verify.fingerprint(t, k) == fp, "multiset changed"
+    del ws, t
+    torch.cuda.empty_cache()
+
+
+def test_config2_1b_u64_properties(cuda):  # BASELINE.json configs[1]
+    _property_run("u64", 1_000_000_000, distr.Distr.UNIFORM, 0, cuda)
+
+
+@pytest.mark.parametrize("kind,dist,param", [("f32", distr.Distr.FLOAT_TEST, 1 << 20), ("f64", distr.Distr.UNIFORM, 0),
+                                             ("i32", distr.Distr.UNIFORM, 0), ("i64", distr.Distr.UNIFORM, 0)])
+def test_config3_transform_kinds_properties(kind, dist, param, cuda):  # configs[2] at 2^28 keys
+    _property_run(kind, 1 << 28, dist, param, cuda)
+
+
+@pytest.mark.parametrize("dist,param", [(distr.Distr.ZIPF, 1.0), (distr.Distr.STEP, 16), (distr.Distr.ASCENDING, 2_000_000_000)])
+def test_config4_2b_u32_skew_properties(dist, param, cuda):  # configs[3]: n > 2^30 -> two look-back portions
+    _property_run("u32", 2_000_000_000, dist, param, cuda)
+
+
+def test_portion_boundary_small_keys(cuda):
+    # n just over one look-back portion (2^30 elements) with 1-byte keys: cheap
+    # exercise of the bins_out hand-off between portions, checked exactly
+    import torch
+    n = (1 << 30) + 12_345
+    t = torch.empty(n, dtype=torch.uint8, device=cuda)
+    distr.generate(t, rs.Kind.U8, distr.Distr.UNIFORM, 0, seed=9)
+    counts = torch.zeros(256, dtype=torch.int64, device=cuda)
+    step = 1 << 28
+    for lo in range(0, n, step):
+        counts += torch.bincount(t[lo:lo + step].to(torch.int32), minlength=256)
+    rs.radix_sort(t)
+    torch.cuda.synchronize()
+    assert verify.count_unsorted(t, rs.Kind.U8) == 0
+    bounds = torch.cumsum(counts, 0).cpu().numpy()
+    got = t[torch.from_numpy(np.minimum(bounds - 1, n - 1)).to(cuda)].cpu().numpy()
+    present = counts.cpu().numpy() > 0
+    assert (got[present] == np.arange(256)[present]).all()
