@@ -50,11 +50,11 @@ struct VariantDesc { int threads, items, min_blocks; };
 // The table a variant index selects from, per element width.  Index 0 is the
 // default; the others exist for on-GPU sweeps (b200sort_set_variant).
 template <int EB> struct Variants;
-template <> struct Variants<1>  { static constexpr VariantDesc v[] = {{512, 32, 2}, {512, 16, 2}}; };
-template <> struct Variants<2>  { static constexpr VariantDesc v[] = {{512, 24, 2}, {512, 16, 2}}; };
-template <> struct Variants<4>  { static constexpr VariantDesc v[] = {{512, 16, 2}, {512, 22, 2}, {384, 20, 2}, {256, 16, 4}, {512, 12, 2}, {1024, 8, 1}}; };
-template <> struct Variants<8>  { static constexpr VariantDesc v[] = {{512, 12, 2}, {512, 16, 2}, {384, 14, 2}, {256, 16, 4}, {512, 8, 2}, {256, 12, 4}}; };
-template <> struct Variants<16> { static constexpr VariantDesc v[] = {{256, 12, 2}, {512, 8, 2}, {256, 8, 4}}; };
+template <> struct Variants<1>  { static constexpr VariantDesc v[] = {{512, 32, 2}, {512, 16, 2}, {256, 32, 4}}; };
+template <> struct Variants<2>  { static constexpr VariantDesc v[] = {{512, 24, 2}, {512, 16, 2}, {256, 24, 4}}; };
+template <> struct Variants<4>  { static constexpr VariantDesc v[] = {{512, 16, 2}, {512, 22, 2}, {384, 20, 3}, {256, 16, 4}, {256, 22, 4}, {256, 16, 6}, {512, 16, 3}, {1024, 12, 1}}; };
+template <> struct Variants<8>  { static constexpr VariantDesc v[] = {{512, 12, 2}, {512, 16, 2}, {384, 14, 3}, {256, 16, 4}, {256, 12, 4}, {256, 12, 6}, {512, 10, 3}, {1024, 8, 1}}; };
+template <> struct Variants<16> { static constexpr VariantDesc v[] = {{256, 12, 2}, {512, 8, 2}, {256, 8, 4}, {256, 6, 4}}; };
 
 template <int EB> constexpr int num_variants() { return (int)(sizeof(Variants<EB>::v) / sizeof(VariantDesc)); }
 template <int EB> int min_tile() {
@@ -103,10 +103,10 @@ template <int EB> int current_variant() {
 }
 
 // ---- workspace layout -----------------------------------------------------------
-// [ tmp elements | bins D*P*256 u64 | plan | hist D*256 u64 | tickets D*P u32 | look-back ]
+// [ tmp elements | bins D*P*256 u64 | plan | hist D*256 u64 | tickets D*P u32 | stats | look-back ]
 //                                          ^--------- zeroed by one memset ---------------^
 struct Layout {
-    size_t tmp_off, bins_off, plan_off, hist_off, ticket_off, lb_off, total;
+    size_t tmp_off, bins_off, plan_off, hist_off, ticket_off, stats_off, lb_off, total;
     size_t zero_off, zero_bytes;
     int portions;
     size_t portion_elems;  // elements per portion (multiple of tile)
@@ -130,6 +130,7 @@ Layout make_layout(size_t n, size_t elem_bytes, int digits, int tile) {
     L.plan_off = off;   off = align_up(off + sizeof(Plan), 256);
     L.hist_off = off;   off = align_up(off + (size_t)digits * RADIX * 8, 256);
     L.ticket_off = off; off = align_up(off + (size_t)digits * L.portions * 4, 256);
+    L.stats_off = off;  off += 256;
     L.lb_off = off;     off = align_up(off + (size_t)digits * L.tiles_total * RADIX * 4, 256);
     L.total = off;
     L.zero_off = L.hist_off;
@@ -181,6 +182,7 @@ int sort_device_impl(typename Tr::elem_t* d_elems, void* d_tmp, size_t tmp_bytes
     unsigned long long* hist = reinterpret_cast<unsigned long long*>(ws + L.hist_off);
     uint32_t* tickets = reinterpret_cast<uint32_t*>(ws + L.ticket_off);
     uint32_t* lookback = reinterpret_cast<uint32_t*>(ws + L.lb_off);
+    uint32_t* stats = reinterpret_cast<uint32_t*>(ws + L.stats_off);
 
     PhaseTimer timer(out_ms != nullptr, st);
     timer.mark();
@@ -229,6 +231,7 @@ int sort_device_impl(typename Tr::elem_t* d_elems, void* d_tmp, size_t tmp_bytes
             a.bins_out = (q + 1 < L.portions) ? bins + ((size_t)p * L.portions + q + 1) * RADIX : nullptr;
             a.lookback = lookback + lb_cursor * RADIX;
             a.ticket = tickets + (size_t)p * L.portions + q;
+            a.stats = stats;
             a.prm = prm;
             lb_cursor += a.num_tiles;
             CU((launch_pass_idx<Tr, EB, 0>(variant, a, st)));

@@ -64,9 +64,13 @@ __device__ __forceinline__ u128 ld_elem<u128>(const u128* p) {
 
 // ---------------------------------------------------------------------------
 // K1: all-digit histogram.  16-byte coalesced loads (LDG.128), four in flight
-// per thread; one privatised shared-memory histogram set per CTA; a digit that
-// is identical across the converged warp (constant high bytes, few-unique
-// inputs) costs one shared atomic per warp instead of 32 same-address ones.
+// per thread; one privatised shared-memory histogram set per CTA, bumped with
+// no-return shared atomics.  Measured on B200 (profiles/r01_microbench_*.txt):
+// a no-return ATOMS costs 1.2-1.6 cycles per warp instruction whether the 32
+// lanes hit 256 different bins or all the same one -- the unit aggregates
+// same-address lanes itself -- so skewed inputs (constant high bytes, few-unique)
+// need no software warp aggregation; ballot/match aggregation only added ADU
+// and branch work (r01 ncu: 68 instructions per 32 keys, 21 % of HBM peak).
 // ---------------------------------------------------------------------------
 template <typename Tr, int THREADS>
 __global__ void __launch_bounds__(THREADS)
@@ -82,19 +86,8 @@ hist_all_digits_kernel(const typename Tr::elem_t* __restrict__ in, size_t n,
 
     auto count = [&](E raw) {
         const E e = Tr::xform_in(raw, prm);
-        const unsigned active = __activemask();
-        const int leader = __ffs(active) - 1;
-        const unsigned lane = tid & 31;
 #pragma unroll
-        for (int p = 0; p < D; ++p) {
-            const unsigned d = Tr::digit(e, p, prm);
-            const unsigned d0 = __shfl_sync(active, d, leader);
-            if (__all_sync(active, d == d0)) {
-                if ((int)lane == leader) atomicAdd(&sh[p * RADIX + d0], (uint32_t)__popc(active));
-            } else {
-                atomicAdd(&sh[p * RADIX + d], 1u);
-            }
-        }
+        for (int p = 0; p < D; ++p) atomicAdd(&sh[p * RADIX + Tr::digit(e, p, prm)], 1u);
     };
     auto count_vec = [&](uint4 v) {
         union { uint4 v; E e[VEC]; } u;
@@ -181,6 +174,24 @@ scan_plan_kernel(const unsigned long long* __restrict__ hist, unsigned long long
 
 // ---------------------------------------------------------------------------
 // K3: one digit pass over one portion (< 2^30 elements), onesweep style.
+//
+// Ranking.  Measured on B200 (profiles/r01_microbench_*.txt, r01 ncu capture):
+// MATCH.ANY on 8-bit digits costs 41-47 cycles per warp instruction per SM (ADU
+// pipe, ~1 cycle per distinct value) and capped the first version of this kernel
+// at 0.46 keys/cycle/SM; a shared-memory atomicAdd WITH return costs 1.85.  So a
+// key's rank inside its warp is simply the value its atomicAdd on the warp's
+// digit counter returns.  That is a correct LSD pass iff lanes of one warp
+// instruction that hit the same counter are served in ascending lane order: true
+// in 3e10 checked lane-rounds on B200 (profiles/r01_microbench_atomics_order.txt)
+// but not an architectural promise, so the kernel does not rely on it:
+//   * key-only sorts need less than stability -- equal keys are bit-identical, so
+//     a pass is correct iff same-digit keys stay ordered by their LOWER digits.
+//     The write-out loop checks exactly that on the digit-sorted tile in shared
+//     memory (one extra neighbour read per key); a tile that fails is re-ranked
+//     with the ballot path below and rewritten, and counted in stats[0].
+//   * records (NEEDS_STABLE) always use the ballot path: 8 ballots give the lanes
+//     holding the same digit, rank = leader's counter + lower lanes in the group,
+//     lane-ordered by construction.
 // ---------------------------------------------------------------------------
 template <typename Tr>
 struct PassArgs {
@@ -195,6 +206,7 @@ struct PassArgs {
     unsigned long long* bins_out;        // [256] base for the next portion (or null)
     uint32_t* lookback;                  // [num_tiles][256] status words, zeroed
     uint32_t* ticket;                    // tile-id dispenser, zeroed
+    uint32_t* stats;                     // [0] tiles that took the re-rank fallback
     typename Tr::Params prm;
 };
 
@@ -208,6 +220,44 @@ struct PassSmem {
     static constexpr size_t EXCL_BYTES = (size_t)RADIX * sizeof(uint32_t);
     static constexpr size_t TOTAL = HIST_BYTES + TILE_BYTES + GOFF_BYTES + EXCL_BYTES + 64;
 };
+
+// lane-ordered rank of one item inside its warp: 8 ballots -> lanes with my digit
+template <bool FULL_TILE>
+__device__ __forceinline__ uint32_t ballot_rank(unsigned d, bool valid, uint32_t* my_hist, int lane, unsigned lane_lt) {
+    unsigned m = FULL_TILE ? FULL_MASK : __ballot_sync(FULL_MASK, valid);
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const unsigned bal = __ballot_sync(FULL_MASK, bit);
+        m &= bit ? bal : ~bal;
+    }
+    const int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(&my_hist[d], (uint32_t)__popc(m));
+    base = __shfl_sync(FULL_MASK, base, leader & 31);
+    return base + __popc(m & lane_lt);
+}
+
+// Thread d owns digit d: turn the per-warp counts of column d into per-warp
+// bases inside the digit-sorted tile (block-exclusive offset of the digit +
+// counts of the warps before).  Returns the tile's count of digit d.
+template <int WARPS>
+__device__ __forceinline__ uint32_t column_total(const uint32_t* warp_hist, int d) {
+    uint32_t c = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) c += warp_hist[w * RADIX + d];
+    return c;
+}
+template <int WARPS>
+__device__ __forceinline__ void column_bases(uint32_t* warp_hist, int d, uint32_t start) {
+    uint32_t run = start;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) {
+        const uint32_t t = warp_hist[w * RADIX + d];
+        warp_hist[w * RADIX + d] = run;
+        run += t;
+    }
+}
 
 template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
@@ -226,7 +276,7 @@ onesweep_pass_kernel(const PassArgs<Tr> a) {
     uint32_t* warp_hist = reinterpret_cast<uint32_t*>(smem_raw + SM::TILE_BYTES);
     long long* goff = reinterpret_cast<long long*>(smem_raw + SM::TILE_BYTES + SM::HIST_BYTES);
     uint32_t* s_excl = reinterpret_cast<uint32_t*>(smem_raw + SM::TILE_BYTES + SM::HIST_BYTES + SM::GOFF_BYTES);
-    uint32_t* s_misc = s_excl + RADIX;  // [0] ticket, [1..] warp totals of the digit scan
+    uint32_t* s_misc = s_excl + RADIX;  // [0] ticket, [1..8] warp totals of the digit scan
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lane_lt = (1u << lane) - 1u;
@@ -264,26 +314,32 @@ onesweep_pass_kernel(const PassArgs<Tr> a) {
         for (int i = 0; i < ITEMS; ++i) e[i] = Tr::xform_in(e[i], a.prm);
     }
 
-    // ---- early counts: per-warp digit histograms by shared atomics
+    // ---- rank inside the warp; the warp's counters end up holding its histogram
     uint32_t* my_hist = warp_hist + warp * RADIX;
+    uint32_t rank[ITEMS];
+    if (Tr::NEEDS_STABLE) {
+        if (full) {
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i)
-        if (full || wbase + i * 32 < tile_n) atomicAdd(&my_hist[Tr::digit(e[i], pass, a.prm)], 1u);
+            for (int i = 0; i < ITEMS; ++i)
+                rank[i] = ballot_rank<true>(Tr::digit(e[i], pass, a.prm), true, my_hist, lane, lane_lt);
+        } else {
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i)
+                rank[i] = ballot_rank<false>(Tr::digit(e[i], pass, a.prm), wbase + i * 32 < tile_n, my_hist, lane, lane_lt);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+            if (full || wbase + i * 32 < tile_n) rank[i] = atomicAdd(&my_hist[Tr::digit(e[i], pass, a.prm)], 1u);
+    }
     __syncthreads();
 
-    // ---- thread d owns digit d: column-reduce the warp histograms into
-    // exclusive-over-warps prefixes, publish the tile's count, scan over digits
+    // ---- thread d owns digit d: tile count -> publish -> scan over digits ->
+    // per-warp bases inside the digit-sorted tile
     uint32_t count = 0;
     uint32_t* lb = a.lookback + (size_t)tile * RADIX;
     if (tid < RADIX) {
-        uint32_t run = 0;
-#pragma unroll
-        for (int w = 0; w < WARPS; ++w) {
-            const uint32_t t = warp_hist[w * RADIX + tid];
-            warp_hist[w * RADIX + tid] = run;
-            run += t;
-        }
-        count = run;
+        count = column_total<WARPS>(warp_hist, tid);
         st_relaxed_u32(lb + tid, (tile == 0 ? LB_FLAG_INCLUSIVE : LB_FLAG_PARTIAL) | count);
     }
     uint32_t incl = count;
@@ -294,32 +350,21 @@ onesweep_pass_kernel(const PassArgs<Tr> a) {
     }
     if (lane == 31 && warp < RADIX / 32) s_misc[1 + warp] = incl;
     __syncthreads();
+    uint32_t excl = 0;
     if (tid < RADIX) {
         uint32_t base = 0;
 #pragma unroll
         for (int w = 0; w < RADIX / 32; ++w) base += (w < warp) ? s_misc[1 + w] : 0u;
-        s_excl[tid] = base + incl - count;  // keys of the tile with a smaller digit
+        excl = base + incl - count;  // keys of the tile with a smaller digit
+        s_excl[tid] = excl;
+        column_bases<WARPS>(warp_hist, tid, excl);
     }
     __syncthreads();
 
-    // ---- rank: __match_any_sync groups the lanes holding the same digit; the
-    // lowest lane of a group bumps the warp's running counter for the group
-    uint32_t rank[ITEMS];
+    // ---- tile-local sort: every key goes to its slot of the digit-sorted tile
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-        const unsigned d = Tr::digit(e[i], pass, a.prm);
-        unsigned m = __match_any_sync(FULL_MASK, d);
-        if (!full) m &= __ballot_sync(FULL_MASK, wbase + i * 32 < tile_n);
-        const int leader = __ffs(m) - 1;
-        uint32_t old = 0;
-        if (lane == leader) {
-            old = my_hist[d];
-            my_hist[d] = old + __popc(m);
-        }
-        old = __shfl_sync(FULL_MASK, old, leader & 31);
-        rank[i] = old + __popc(m & lane_lt) + s_excl[d];
-        __syncwarp();
-    }
+    for (int i = 0; i < ITEMS; ++i)
+        if (full || wbase + i * 32 < tile_n) tile_s[rank[i] + my_hist[Tr::digit(e[i], pass, a.prm)]] = e[i];
 
     // ---- decoupled look-back (digit threads): sum the counts of preceding
     // tiles until one that already knows its inclusive prefix
@@ -339,14 +384,46 @@ onesweep_pass_kernel(const PassArgs<Tr> a) {
             excl_tiles = sum;
         }
         const unsigned long long gbase = a.bins_in[tid] + excl_tiles;
-        goff[tid] = (long long)gbase - (long long)s_excl[tid];
+        goff[tid] = (long long)gbase - (long long)excl;
         if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[tid] = gbase + count;
     }
+    __syncthreads();
 
-    // ---- tile-local sort in shared memory, then coalesced run write-out
+    // ---- coalesced run write-out; key-only passes check the order of the tile
+    const bool verify = !Tr::NEEDS_STABLE && pass > 0;
+    bool bad = false;
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const uint32_t idx = (uint32_t)j * THREADS + tid;
+        if (full || idx < tile_n) {
+            E v = tile_s[idx];
+            const unsigned d = Tr::digit(v, pass, a.prm);
+            if (verify && idx + 1 < tile_n) {
+                const E nx = tile_s[idx + 1];
+                bad |= (Tr::digit(nx, pass, a.prm) == d) && Tr::low_less(nx, v, pass, a.prm);
+            }
+            if (pp.xf_out) v = Tr::xform_out(v, a.prm);
+            dst[goff[d] + (long long)idx] = v;
+        }
+    }
+    if (!verify) return;
+    if (!__syncthreads_or(bad)) return;
+
+    // ---- fallback (never taken on hardware whose shared atomics are lane-ordered):
+    // re-rank with ballots, rebuild the tile, rewrite the same output slots
+    if (tid == 0) atomicAdd(a.stats, 1u);
+#pragma unroll
+    for (int i = tid; i < WARPS * RADIX; i += THREADS) warp_hist[i] = 0;
+    __syncthreads();
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i)
-        if (full || wbase + i * 32 < tile_n) tile_s[rank[i]] = e[i];
+        rank[i] = ballot_rank<false>(Tr::digit(e[i], pass, a.prm), full || wbase + i * 32 < tile_n, my_hist, lane, lane_lt);
+    __syncthreads();
+    if (tid < RADIX) column_bases<WARPS>(warp_hist, tid, excl);
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i)
+        if (full || wbase + i * 32 < tile_n) tile_s[rank[i] + my_hist[Tr::digit(e[i], pass, a.prm)]] = e[i];
     __syncthreads();
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {

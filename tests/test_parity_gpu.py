@@ -222,7 +222,7 @@ def test_demo_shapes_pairs_payload_zero(cuda):
 
 # ---- kernel variants, alignment, re-entrancy, graphs --------------------------------
 
-@pytest.mark.parametrize("kind,kb,nvar", [("u8", 1, 2), ("u16", 2, 2), ("u32", 4, 6), ("u64", 8, 6), ("u128", 16, 3)])
+@pytest.mark.parametrize("kind,kb,nvar", [("u8", 1, 3), ("u16", 2, 3), ("u32", 4, 8), ("u64", 8, 8), ("u128", 16, 4)])
 def test_every_kernel_variant(kind, kb, nvar, cuda):
     a = _ref.random_keys(kind, 777_777, seed=3)
     try:
