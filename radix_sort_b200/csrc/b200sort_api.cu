@@ -6,6 +6,7 @@
 // either launches the sm_100a kernels or returns an error.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <atomic>
 #include <cstdio>
 #include <cstring>
@@ -50,11 +51,11 @@ struct VariantDesc { int threads, items, min_blocks; };
 // The table a variant index selects from, per element width.  Index 0 is the
 // default; the others exist for on-GPU sweeps (b200sort_set_variant).
 template <int EB> struct Variants;
-template <> struct Variants<1>  { static constexpr VariantDesc v[] = {{512, 32, 2}, {512, 16, 2}, {256, 32, 4}}; };
-template <> struct Variants<2>  { static constexpr VariantDesc v[] = {{512, 24, 2}, {512, 16, 2}, {256, 24, 4}}; };
-template <> struct Variants<4>  { static constexpr VariantDesc v[] = {{512, 16, 2}, {512, 22, 2}, {384, 20, 3}, {256, 16, 4}, {256, 22, 4}, {256, 16, 6}, {512, 16, 3}, {1024, 12, 1}}; };
-template <> struct Variants<8>  { static constexpr VariantDesc v[] = {{512, 12, 2}, {512, 16, 2}, {384, 14, 3}, {256, 16, 4}, {256, 12, 4}, {256, 12, 6}, {512, 10, 3}, {1024, 8, 1}}; };
-template <> struct Variants<16> { static constexpr VariantDesc v[] = {{256, 12, 2}, {512, 8, 2}, {256, 8, 4}, {256, 6, 4}}; };
+template <> struct Variants<1>  { static constexpr VariantDesc v[] = {{512, 32, 2}, {512, 16, 3}, {256, 32, 4}}; };
+template <> struct Variants<2>  { static constexpr VariantDesc v[] = {{512, 24, 2}, {512, 16, 3}, {256, 24, 4}}; };
+template <> struct Variants<4>  { static constexpr VariantDesc v[] = {{512, 16, 2}, {512, 22, 2}, {512, 16, 3}, {512, 12, 4}, {256, 16, 6}, {256, 24, 4}, {384, 20, 3}, {1024, 12, 1}}; };
+template <> struct Variants<8>  { static constexpr VariantDesc v[] = {{512, 12, 2}, {512, 16, 2}, {512, 10, 3}, {512, 8, 4}, {256, 12, 6}, {256, 16, 4}, {384, 12, 3}, {1024, 8, 1}}; };
+template <> struct Variants<16> { static constexpr VariantDesc v[] = {{256, 12, 2}, {512, 8, 2}, {256, 8, 4}, {512, 6, 2}}; };
 
 template <int EB> constexpr int num_variants() { return (int)(sizeof(Variants<EB>::v) / sizeof(VariantDesc)); }
 template <int EB> int min_tile() {
@@ -194,12 +195,20 @@ int sort_device_impl(typename Tr::elem_t* d_elems, void* d_tmp, size_t tmp_bytes
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         constexpr int HT = 512;
+        constexpr size_t HS = HistCfg<Tr>::SMEM;
+        auto hk = hist_all_digits_kernel<Tr, HT>;
+        static std::atomic<unsigned> configured{0};  // bit per device
+        if (HS > 48 * 1024 && !(configured.load(std::memory_order_acquire) & (1u << (dev & 31)))) {
+            CU(cudaFuncSetAttribute(hk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HS));
+            configured.fetch_or(1u << (dev & 31), std::memory_order_release);
+        }
+        const size_t per_sm = std::max<size_t>(1, std::min<size_t>(4, (220 * 1024) / HS));
         const size_t vecs = (n * EB + 15) / 16;
         size_t blocks = (vecs + (size_t)HT * 4 - 1) / ((size_t)HT * 4);
-        const size_t cap = (size_t)sms * 4;
+        const size_t cap = (size_t)sms * per_sm;
         if (blocks > cap) blocks = cap;
         if (blocks < 1) blocks = 1;
-        hist_all_digits_kernel<Tr, HT><<<(unsigned)blocks, HT, 0, st>>>(d_elems, n, hist, prm);
+        hk<<<(unsigned)blocks, HT, HS, st>>>(d_elems, n, hist, prm);
         g_launches.fetch_add(1, std::memory_order_relaxed);
         CU(cudaGetLastError());
     }

@@ -88,20 +88,21 @@ __host__ __device__ __forceinline__ bool ordered_less<u128>(u128 a, u128 b) {
 template <>
 __host__ __device__ __forceinline__ unsigned long long low64<u128>(u128 k) { return k.lo; }
 
-// low_less(a, b, pass): compare only the bits BELOW digit `pass` of two ordered
-// keys (the part earlier passes have already sorted by).  pass >= 1.
+// prefix_less(a, b, pass): compare two ordered keys on digits 0..pass only (the
+// bits above digit `pass` are shifted out).  A tile that a pass has sorted by
+// digit `pass` is correctly ordered iff this never holds for (next, current).
 template <typename U>
-__host__ __device__ __forceinline__ bool low_less(U a, U b, int pass) {
-    const int sh = (int)sizeof(U) * 8 - 8 * pass;
+__host__ __device__ __forceinline__ bool prefix_less(U a, U b, int pass) {
+    const int sh = (int)sizeof(U) * 8 - 8 * (pass + 1);
     return (U)(a << sh) < (U)(b << sh);
 }
 template <>
-__host__ __device__ __forceinline__ bool low_less<u128>(u128 a, u128 b, int pass) {
-    if (pass <= 8) {
-        const int sh = 64 - 8 * pass;  // pass == 8: whole low word
+__host__ __device__ __forceinline__ bool prefix_less<u128>(u128 a, u128 b, int pass) {
+    if (pass < 8) {
+        const int sh = 64 - 8 * (pass + 1);
         return (a.lo << sh) < (b.lo << sh);
     }
-    const int sh = 128 - 8 * pass;
+    const int sh = 128 - 8 * (pass + 1);
     const unsigned long long ah = a.hi << sh, bh = b.hi << sh;
     return ah < bh || (ah == bh && a.lo < b.lo);
 }
@@ -127,7 +128,7 @@ struct KeyTraits {
     // the order of their lower digits -- which K3 can check exactly (sort_kernels.cuh)
     static constexpr bool NEEDS_STABLE = false;
     struct Params {};
-    __device__ __forceinline__ static bool low_less(elem_t a, elem_t b, int pass, const Params&) { return b200::low_less<U>(a, b, pass); }
+    __device__ __forceinline__ static bool prefix_less(elem_t a, elem_t b, int pass, const Params&) { return b200::prefix_less<U>(a, b, pass); }
     __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params&) { return to_ordered<U, XF_>(e); }
     __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params&) { return from_ordered<U, XF_>(e); }
     __device__ __forceinline__ static unsigned digit(elem_t e, int pass, const Params&) { return digit_of<U>(e, pass); }
@@ -149,7 +150,7 @@ struct PartitionTraits {
         U spl[MAX_SPLITTERS];
         int nsplit;
     };
-    __device__ __forceinline__ static bool low_less(elem_t, elem_t, int, const Params&) { return false; }
+    __device__ __forceinline__ static bool prefix_less(elem_t, elem_t, int, const Params&) { return false; }
     __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params&) { return e; }
     __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params&) { return e; }
     __device__ __forceinline__ static unsigned digit(elem_t e, int, const Params& p) {
@@ -176,7 +177,7 @@ struct RecordTraits<unsigned long long, K, XF_> {  // 8-byte record, 4-byte key
     static constexpr int DIGITS = (int)sizeof(K);
     static constexpr bool NEEDS_STABLE = true;  // payloads make the order of equal keys observable (tests.rs:175-187)
     struct Params { int key_shift; };
-    __device__ __forceinline__ static bool low_less(elem_t, elem_t, int, const Params&) { return false; }
+    __device__ __forceinline__ static bool prefix_less(elem_t, elem_t, int, const Params&) { return false; }
     __device__ __forceinline__ static K key(elem_t e, const Params& p) { return (K)(e >> p.key_shift); }
     __device__ __forceinline__ static elem_t with_key(elem_t e, K k, const Params& p) {
         const elem_t mask = (elem_t)(K)~(K)0 << p.key_shift;
@@ -202,7 +203,7 @@ struct RecordTraits<u128, unsigned long long, XF_> {  // 16-byte record, 8-byte 
     static constexpr int DIGITS = 8;
     static constexpr bool NEEDS_STABLE = true;
     struct Params { int key_shift; };  // 0 -> key in .lo, 64 -> key in .hi
-    __device__ __forceinline__ static bool low_less(elem_t, elem_t, int, const Params&) { return false; }
+    __device__ __forceinline__ static bool prefix_less(elem_t, elem_t, int, const Params&) { return false; }
     __device__ __forceinline__ static key_t key(elem_t e, const Params& p) { return p.key_shift ? e.hi : e.lo; }
     __device__ __forceinline__ static elem_t with_key(elem_t e, key_t k, const Params& p) {
         if (p.key_shift) e.hi = k; else e.lo = k;

@@ -65,29 +65,38 @@ __device__ __forceinline__ u128 ld_elem<u128>(const u128* p) {
 // ---------------------------------------------------------------------------
 // K1: all-digit histogram.  16-byte coalesced loads (LDG.128), four in flight
 // per thread; one privatised shared-memory histogram set per CTA, bumped with
-// no-return shared atomics.  Measured on B200 (profiles/r01_microbench_*.txt):
-// a no-return ATOMS costs 1.2-1.6 cycles per warp instruction whether the 32
-// lanes hit 256 different bins or all the same one -- the unit aggregates
-// same-address lanes itself -- so skewed inputs (constant high bytes, few-unique)
-// need no software warp aggregation; ballot/match aggregation only added ADU
-// and branch work (r01 ncu: 68 instructions per 32 keys, 21 % of HBM peak).
+// no-return shared atomics.  Measured on B200 (profiles/r01_*): a no-return ATOMS
+// is not slowed by same-address lanes (the unit merges them), so skewed inputs
+// need no software warp aggregation -- the ballot/branch version of this kernel
+// spent 68 instructions per 32 keys for 21 % of HBM peak.  What does cost is bank
+// conflicts between DIFFERENT digits (3.2 wavefronts per atomic with one table),
+// so every bin is replicated R times with the copy chosen by lane % R: lanes
+// l, l+R, ... collide only if their digits are congruent mod 32/R.
 // ---------------------------------------------------------------------------
+template <typename Tr>
+struct HistCfg {
+    static constexpr int R = Tr::DIGITS <= 8 ? 8 : 4;
+    static constexpr size_t SMEM = (size_t)Tr::DIGITS * RADIX * R * sizeof(uint32_t);
+};
+
 template <typename Tr, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 hist_all_digits_kernel(const typename Tr::elem_t* __restrict__ in, size_t n,
                        unsigned long long* __restrict__ hist, typename Tr::Params prm) {
     using E = typename Tr::elem_t;
     constexpr int D = Tr::DIGITS;
+    constexpr int R = HistCfg<Tr>::R;
     constexpr int VEC = 16 / (int)sizeof(E);
-    __shared__ uint32_t sh[D * RADIX];
+    extern __shared__ __align__(16) uint32_t hist_sh[];
     const int tid = threadIdx.x;
-    for (int i = tid; i < D * RADIX; i += THREADS) sh[i] = 0;
+    for (int i = tid; i < D * RADIX * R; i += THREADS) hist_sh[i] = 0;
     __syncthreads();
+    uint32_t* mine = hist_sh + (tid & (R - 1));
 
     auto count = [&](E raw) {
         const E e = Tr::xform_in(raw, prm);
 #pragma unroll
-        for (int p = 0; p < D; ++p) atomicAdd(&sh[p * RADIX + Tr::digit(e, p, prm)], 1u);
+        for (int p = 0; p < D; ++p) atomicAdd(&mine[(p * RADIX + Tr::digit(e, p, prm)) * R], 1u);
     };
     auto count_vec = [&](uint4 v) {
         union { uint4 v; E e[VEC]; } u;
@@ -120,7 +129,9 @@ hist_all_digits_kernel(const typename Tr::elem_t* __restrict__ in, size_t n,
     }
     __syncthreads();
     for (int k = tid; k < D * RADIX; k += THREADS) {
-        const uint32_t c = sh[k];
+        uint32_t c = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) c += hist_sh[k * R + r];
         if (c) atomicAdd(&hist[k], (unsigned long long)c);
     }
 }
@@ -175,22 +186,27 @@ scan_plan_kernel(const unsigned long long* __restrict__ hist, unsigned long long
 // ---------------------------------------------------------------------------
 // K3: one digit pass over one portion (< 2^30 elements), onesweep style.
 //
-// Ranking.  Measured on B200 (profiles/r01_microbench_*.txt, r01 ncu capture):
+// Ranking.  Measured on B200 (profiles/r01_microbench_*.txt, r01 ncu captures):
 // MATCH.ANY on 8-bit digits costs 41-47 cycles per warp instruction per SM (ADU
 // pipe, ~1 cycle per distinct value) and capped the first version of this kernel
-// at 0.46 keys/cycle/SM; a shared-memory atomicAdd WITH return costs 1.85.  So a
-// key's rank inside its warp is simply the value its atomicAdd on the warp's
-// digit counter returns.  That is a correct LSD pass iff lanes of one warp
-// instruction that hit the same counter are served in ascending lane order: true
-// in 3e10 checked lane-rounds on B200 (profiles/r01_microbench_atomics_order.txt)
-// but not an architectural promise, so the kernel does not rely on it:
+// at 0.46 keys/cycle/SM; a shared-memory atomicAdd costs ~3.5 wavefronts.  So:
+//   1. count:   every key bumps its warp's private counter of its digit (no return);
+//   2. bases:   thread d turns column d of the warp counters into each warp's first
+//               slot for digit d inside the digit-sorted tile, and publishes the
+//               tile's count of d for the look-back;
+//   3. scatter: a second atomicAdd, WITH return, hands every key its final slot in
+//               the tile in shared memory -- no per-key rank registers at all.
+// Step 3 is a correct LSD pass iff the lanes of one warp instruction that hit the
+// same counter are served in ascending lane order: true in 3e10 checked
+// lane-rounds on B200 (profiles/r01_microbench_atomics_order.txt) but not an
+// architectural promise, so the kernel does not rely on it:
 //   * key-only sorts need less than stability -- equal keys are bit-identical, so
-//     a pass is correct iff same-digit keys stay ordered by their LOWER digits.
-//     The write-out loop checks exactly that on the digit-sorted tile in shared
-//     memory (one extra neighbour read per key); a tile that fails is re-ranked
-//     with the ballot path below and rewritten, and counted in stats[0].
-//   * records (NEEDS_STABLE) always use the ballot path: 8 ballots give the lanes
-//     holding the same digit, rank = leader's counter + lower lanes in the group,
+//     a pass is correct iff the digit-sorted tile is non-decreasing on digits
+//     0..pass.  The write-out loop checks exactly that (one neighbour read per
+//     key); a tile that fails is re-ranked by rerank_tile() and rewritten, and
+//     counted in stats[0].
+//   * records (NEEDS_STABLE) always rank with ballots: 8 ballots give the lanes
+//     holding the same digit, rank = leader's counter + lower lanes of the group,
 //     lane-ordered by construction.
 // ---------------------------------------------------------------------------
 template <typename Tr>
@@ -214,11 +230,32 @@ template <typename Tr, int THREADS, int ITEMS>
 struct PassSmem {
     static constexpr int WARPS = THREADS / 32;
     static constexpr int TILE = THREADS * ITEMS;
-    static constexpr size_t HIST_BYTES = (size_t)WARPS * RADIX * sizeof(uint32_t);
     static constexpr size_t TILE_BYTES = (size_t)TILE * sizeof(typename Tr::elem_t);
-    static constexpr size_t GOFF_BYTES = (size_t)RADIX * sizeof(long long);
+    static constexpr size_t HIST_BYTES = (size_t)WARPS * RADIX * sizeof(uint32_t);
+    static constexpr size_t GPTR_BYTES = (size_t)RADIX * sizeof(unsigned long long);
     static constexpr size_t EXCL_BYTES = (size_t)RADIX * sizeof(uint32_t);
-    static constexpr size_t TOTAL = HIST_BYTES + TILE_BYTES + GOFF_BYTES + EXCL_BYTES + 64;
+    static constexpr size_t CNT_BYTES = (size_t)RADIX * sizeof(uint32_t);
+    static constexpr size_t TOTAL = TILE_BYTES + HIST_BYTES + GPTR_BYTES + EXCL_BYTES + CNT_BYTES + 64;
+};
+
+// views into the dynamic shared memory of one CTA
+template <typename Tr, int THREADS, int ITEMS>
+struct PassShared {
+    using SM = PassSmem<Tr, THREADS, ITEMS>;
+    typename Tr::elem_t* tile;      // [TILE]   digit-sorted tile
+    uint32_t* warp_hist;            // [WARPS][256] per-warp digit counters
+    unsigned long long* gptr;       // [256] byte address in dst of slot 0 of the tile, per digit
+    uint32_t* excl;                 // [256] keys of the tile with a smaller digit
+    uint32_t* cnt;                  // [256] keys of the tile with this digit
+    uint32_t* misc;                 // [0] ticket, [1..8] warp totals of the digit scan
+    __device__ __forceinline__ explicit PassShared(unsigned char* raw) {
+        tile = reinterpret_cast<typename Tr::elem_t*>(raw);
+        warp_hist = reinterpret_cast<uint32_t*>(raw + SM::TILE_BYTES);
+        gptr = reinterpret_cast<unsigned long long*>(raw + SM::TILE_BYTES + SM::HIST_BYTES);
+        excl = reinterpret_cast<uint32_t*>(raw + SM::TILE_BYTES + SM::HIST_BYTES + SM::GPTR_BYTES);
+        cnt = excl + RADIX;
+        misc = cnt + RADIX;
+    }
 };
 
 // lane-ordered rank of one item inside its warp: 8 ballots -> lanes with my digit
@@ -238,9 +275,7 @@ __device__ __forceinline__ uint32_t ballot_rank(unsigned d, bool valid, uint32_t
     return base + __popc(m & lane_lt);
 }
 
-// Thread d owns digit d: turn the per-warp counts of column d into per-warp
-// bases inside the digit-sorted tile (block-exclusive offset of the digit +
-// counts of the warps before).  Returns the tile's count of digit d.
+// Thread d owns digit d: the tile's count of d, and the per-warp first slots.
 template <int WARPS>
 __device__ __forceinline__ uint32_t column_total(const uint32_t* warp_hist, int d) {
     uint32_t c = 0;
@@ -259,87 +294,115 @@ __device__ __forceinline__ void column_bases(uint32_t* warp_hist, int d, uint32_
     }
 }
 
-template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS>
-__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
-onesweep_pass_kernel(const PassArgs<Tr> a) {
+// coalesced run write-out of the digit-sorted tile; VERIFY adds the order check
+template <typename Tr, int THREADS, int ITEMS, bool FULL, bool VERIFY>
+__device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& sh, const PassArgs<Tr>& a,
+                                          const PassPlan& pp, uint32_t tile_n, int tid) {
     using E = typename Tr::elem_t;
-    using SM = PassSmem<Tr, THREADS, ITEMS>;
-    constexpr int WARPS = SM::WARPS;
-    constexpr int TILE = SM::TILE;
-    static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit needed");
+    bool bad = false;
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const uint32_t idx = (uint32_t)j * THREADS + tid;
+        if (FULL || idx < tile_n) {
+            E v = sh.tile[idx];
+            if (VERIFY && (idx + 1 < (FULL ? (uint32_t)(THREADS * ITEMS) : tile_n)))
+                bad |= Tr::prefix_less(sh.tile[idx + 1], v, a.pass, a.prm);
+            const unsigned d = Tr::digit(v, a.pass, a.prm);
+            if (pp.xf_out) v = Tr::xform_out(v, a.prm);
+            *reinterpret_cast<E*>(sh.gptr[d] + (unsigned long long)idx * sizeof(E)) = v;
+        }
+    }
+    return bad;
+}
 
-    const PassPlan pp = a.plan->pass[a.pass];
-    if (pp.skip) return;
-
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    E* tile_s = reinterpret_cast<E*>(smem_raw);
-    uint32_t* warp_hist = reinterpret_cast<uint32_t*>(smem_raw + SM::TILE_BYTES);
-    long long* goff = reinterpret_cast<long long*>(smem_raw + SM::TILE_BYTES + SM::HIST_BYTES);
-    uint32_t* s_excl = reinterpret_cast<uint32_t*>(smem_raw + SM::TILE_BYTES + SM::HIST_BYTES + SM::GOFF_BYTES);
-    uint32_t* s_misc = s_excl + RADIX;  // [0] ticket, [1..8] warp totals of the digit scan
-
+// Slow path, out of line: rebuild the tile with ballot ranks (lane-ordered by
+// construction) from the keys still in global memory, and rewrite its slots.
+// Entered by a whole CTA; warp_hist may hold anything; excl/gptr are valid.
+template <typename Tr, int THREADS, int ITEMS>
+__device__ __noinline__ void rerank_tile(unsigned char* raw, const PassArgs<Tr>* ap, const typename Tr::elem_t* src_tile,
+                                         uint32_t tile_n, uint32_t xf_in, uint32_t xf_out) {
+    using E = typename Tr::elem_t;
+    constexpr int WARPS = THREADS / 32;
+    const PassArgs<Tr>& a = *ap;
+    PassShared<Tr, THREADS, ITEMS> sh(raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lane_lt = (1u << lane) - 1u;
-    const int pass = a.pass;
-
-    const E* __restrict__ src = (pp.src_is_tmp ? a.tmp : a.keys) + a.portion_off;
-    E* __restrict__ dst = pp.src_is_tmp ? a.keys : a.tmp;
-
-    // tile id from a ticket, not blockIdx: every predecessor a tile may wait on
-    // in the look-back has already started, whatever order CTAs are dispatched in
-    if (tid == 0) s_misc[0] = atomicAdd(a.ticket, 1u);
-#pragma unroll
-    for (int i = tid; i < WARPS * RADIX; i += THREADS) warp_hist[i] = 0;
+    const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
+    uint32_t* my_hist = sh.warp_hist + warp * RADIX;
+    for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
     __syncthreads();
-    const uint32_t tile = s_misc[0];
-    const uint32_t tile_base = tile * (uint32_t)TILE;
-    const uint32_t tile_n = min((uint32_t)TILE, a.portion_n - tile_base);
-    const bool full = (tile_n == (uint32_t)TILE);
+    E e[ITEMS];
+    uint32_t rank[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        const bool valid = wbase + i * 32 < tile_n;
+        if (valid) {
+            e[i] = ld_elem(src_tile + wbase + i * 32);
+            if (xf_in) e[i] = Tr::xform_in(e[i], a.prm);
+        }
+        rank[i] = ballot_rank<false>(Tr::digit(e[i], a.pass, a.prm), valid, my_hist, lane, lane_lt);
+    }
+    __syncthreads();
+    if (tid < RADIX) column_bases<WARPS>(sh.warp_hist, tid, sh.excl[tid]);
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i)
+        if (wbase + i * 32 < tile_n) sh.tile[rank[i] + my_hist[Tr::digit(e[i], a.pass, a.prm)]] = e[i];
+    __syncthreads();
+    PassPlan pp;
+    pp.skip = 0; pp.src_is_tmp = 0; pp.xf_in = xf_in; pp.xf_out = xf_out;
+    write_out<Tr, THREADS, ITEMS, false, false>(sh, a, pp, tile_n, tid);
+}
+
+// One tile, FULL (all THREADS*ITEMS slots valid) known at compile time so the
+// per-key loops carry no bounds predicates.
+template <typename Tr, int THREADS, int ITEMS, bool FULL>
+__device__ __forceinline__ void pass_tile(unsigned char* raw, const PassArgs<Tr>& a, const PassPlan& pp,
+                                          const typename Tr::elem_t* __restrict__ src, typename Tr::elem_t* __restrict__ dst,
+                                          uint32_t tile, uint32_t tile_n) {
+    using E = typename Tr::elem_t;
+    constexpr int WARPS = THREADS / 32;
+    constexpr int TILE = THREADS * ITEMS;
+    constexpr int LB0 = THREADS - RADIX;  // the last 256 threads run the look-back
+    PassShared<Tr, THREADS, ITEMS> sh(raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int pass = a.pass;
+    const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
+    const E* src_tile = src + (size_t)tile * TILE;
 
     // ---- stage: warp-striped load (item i of lane l = element i*32+l of the
-    // warp's contiguous segment), so rank order == memory order
+    // warp's contiguous segment), so slot order == memory order
     E e[ITEMS];
-    const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
-    const E* p = src + tile_base + wbase;
-    if (full) {
 #pragma unroll
-        for (int i = 0; i < ITEMS; ++i) e[i] = ld_elem(p + i * 32);
-    } else {
-#pragma unroll
-        for (int i = 0; i < ITEMS; ++i)
-            if (wbase + i * 32 < tile_n) e[i] = ld_elem(p + i * 32);
-    }
+    for (int i = 0; i < ITEMS; ++i)
+        if (FULL || wbase + i * 32 < tile_n) e[i] = ld_elem(src_tile + wbase + i * 32);
     if (pp.xf_in) {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) e[i] = Tr::xform_in(e[i], a.prm);
     }
 
-    // ---- rank inside the warp; the warp's counters end up holding its histogram
-    uint32_t* my_hist = warp_hist + warp * RADIX;
-    uint32_t rank[ITEMS];
+    // ---- 1. count: the warp's counters become its digit histogram
+    uint32_t* my_hist = sh.warp_hist + warp * RADIX;
+    uint32_t rank[Tr::NEEDS_STABLE ? ITEMS : 1];
     if (Tr::NEEDS_STABLE) {
-        if (full) {
+        const unsigned lane_lt = (1u << lane) - 1u;
 #pragma unroll
-            for (int i = 0; i < ITEMS; ++i)
-                rank[i] = ballot_rank<true>(Tr::digit(e[i], pass, a.prm), true, my_hist, lane, lane_lt);
-        } else {
-#pragma unroll
-            for (int i = 0; i < ITEMS; ++i)
-                rank[i] = ballot_rank<false>(Tr::digit(e[i], pass, a.prm), wbase + i * 32 < tile_n, my_hist, lane, lane_lt);
-        }
+        for (int i = 0; i < ITEMS; ++i)
+            rank[Tr::NEEDS_STABLE ? i : 0] =
+                ballot_rank<FULL>(Tr::digit(e[i], pass, a.prm), FULL || wbase + i * 32 < tile_n, my_hist, lane, lane_lt);
     } else {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
-            if (full || wbase + i * 32 < tile_n) rank[i] = atomicAdd(&my_hist[Tr::digit(e[i], pass, a.prm)], 1u);
+            if (FULL || wbase + i * 32 < tile_n) atomicAdd(&my_hist[Tr::digit(e[i], pass, a.prm)], 1u);
     }
     __syncthreads();
 
-    // ---- thread d owns digit d: tile count -> publish -> scan over digits ->
-    // per-warp bases inside the digit-sorted tile
+    // ---- 2. thread d owns digit d: tile count -> publish -> scan over digits ->
+    // per-warp first slots inside the digit-sorted tile
     uint32_t count = 0;
     uint32_t* lb = a.lookback + (size_t)tile * RADIX;
     if (tid < RADIX) {
-        count = column_total<WARPS>(warp_hist, tid);
+        count = column_total<WARPS>(sh.warp_hist, tid);
         st_relaxed_u32(lb + tid, (tile == 0 ? LB_FLAG_INCLUSIVE : LB_FLAG_PARTIAL) | count);
     }
     uint32_t incl = count;
@@ -348,31 +411,37 @@ onesweep_pass_kernel(const PassArgs<Tr> a) {
         const uint32_t y = __shfl_up_sync(FULL_MASK, incl, o);
         if (lane >= o) incl += y;
     }
-    if (lane == 31 && warp < RADIX / 32) s_misc[1 + warp] = incl;
+    if (lane == 31 && warp < RADIX / 32) sh.misc[1 + warp] = incl;
     __syncthreads();
-    uint32_t excl = 0;
     if (tid < RADIX) {
         uint32_t base = 0;
 #pragma unroll
-        for (int w = 0; w < RADIX / 32; ++w) base += (w < warp) ? s_misc[1 + w] : 0u;
-        excl = base + incl - count;  // keys of the tile with a smaller digit
-        s_excl[tid] = excl;
-        column_bases<WARPS>(warp_hist, tid, excl);
+        for (int w = 0; w < RADIX / 32; ++w) base += (w < warp) ? sh.misc[1 + w] : 0u;
+        const uint32_t excl = base + incl - count;  // keys of the tile with a smaller digit
+        sh.excl[tid] = excl;
+        sh.cnt[tid] = count;
+        column_bases<WARPS>(sh.warp_hist, tid, excl);
     }
     __syncthreads();
 
-    // ---- tile-local sort: every key goes to its slot of the digit-sorted tile
+    // ---- 3. scatter: the returned counter value IS the key's slot in the tile
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i)
-        if (full || wbase + i * 32 < tile_n) tile_s[rank[i] + my_hist[Tr::digit(e[i], pass, a.prm)]] = e[i];
+        if (FULL || wbase + i * 32 < tile_n) {
+            const unsigned d = Tr::digit(e[i], pass, a.prm);
+            const uint32_t slot = Tr::NEEDS_STABLE ? rank[Tr::NEEDS_STABLE ? i : 0] + my_hist[d] : atomicAdd(&my_hist[d], 1u);
+            sh.tile[slot] = e[i];
+        }
 
-    // ---- decoupled look-back (digit threads): sum the counts of preceding
-    // tiles until one that already knows its inclusive prefix
-    if (tid < RADIX) {
+    // ---- decoupled look-back, one digit per thread of the last 256 threads: sum
+    // the counts of preceding tiles until one that knows its inclusive prefix
+    if (tid >= LB0) {
+        const int d = tid - LB0;
+        const uint32_t cnt_d = sh.cnt[d];
         unsigned long long excl_tiles = 0;
         if (tile > 0) {
             uint32_t sum = 0;
-            const uint32_t* q = lb + tid;
+            const uint32_t* q = lb + d;
             for (;;) {
                 q -= RADIX;
                 uint32_t v;
@@ -380,61 +449,56 @@ onesweep_pass_kernel(const PassArgs<Tr> a) {
                 sum += v & LB_VALUE_MASK;
                 if (v & LB_FLAG_INCLUSIVE) break;
             }
-            st_relaxed_u32(lb + tid, LB_FLAG_INCLUSIVE | (sum + count));
+            st_relaxed_u32(lb + d, LB_FLAG_INCLUSIVE | (sum + cnt_d));
             excl_tiles = sum;
         }
-        const unsigned long long gbase = a.bins_in[tid] + excl_tiles;
-        goff[tid] = (long long)gbase - (long long)excl;
-        if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[tid] = gbase + count;
+        const unsigned long long gbase = a.bins_in[d] + excl_tiles;
+        sh.gptr[d] = (unsigned long long)dst + (gbase - sh.excl[d]) * sizeof(E);
+        if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[d] = gbase + cnt_d;
     }
     __syncthreads();
 
     // ---- coalesced run write-out; key-only passes check the order of the tile
-    const bool verify = !Tr::NEEDS_STABLE && pass > 0;
-    bool bad = false;
-#pragma unroll
-    for (int j = 0; j < ITEMS; ++j) {
-        const uint32_t idx = (uint32_t)j * THREADS + tid;
-        if (full || idx < tile_n) {
-            E v = tile_s[idx];
-            const unsigned d = Tr::digit(v, pass, a.prm);
-            if (verify && idx + 1 < tile_n) {
-                const E nx = tile_s[idx + 1];
-                bad |= (Tr::digit(nx, pass, a.prm) == d) && Tr::low_less(nx, v, pass, a.prm);
-            }
-            if (pp.xf_out) v = Tr::xform_out(v, a.prm);
-            dst[goff[d] + (long long)idx] = v;
-        }
+    if (Tr::NEEDS_STABLE || pass == 0) {
+        write_out<Tr, THREADS, ITEMS, FULL, false>(sh, a, pp, tile_n, tid);
+        return;
     }
-    if (!verify) return;
+    const bool bad = write_out<Tr, THREADS, ITEMS, FULL, true>(sh, a, pp, tile_n, tid);
     if (!__syncthreads_or(bad)) return;
-
-    // ---- fallback (never taken on hardware whose shared atomics are lane-ordered):
-    // re-rank with ballots, rebuild the tile, rewrite the same output slots
     if (tid == 0) atomicAdd(a.stats, 1u);
+    rerank_tile<Tr, THREADS, ITEMS>(raw, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
+}
+
+template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
+    using E = typename Tr::elem_t;
+    constexpr int WARPS = THREADS / 32;
+    constexpr int TILE = THREADS * ITEMS;
+    static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit needed");
+
+    const PassPlan pp = a.plan->pass[a.pass];
+    if (pp.skip) return;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    PassShared<Tr, THREADS, ITEMS> sh(smem_raw);
+    const int tid = threadIdx.x;
+
+    const E* __restrict__ src = (pp.src_is_tmp ? a.tmp : a.keys) + a.portion_off;
+    E* __restrict__ dst = pp.src_is_tmp ? a.keys : a.tmp;
+
+    // tile id from a ticket, not blockIdx: every predecessor a tile may wait on
+    // in the look-back has already started, whatever order CTAs are dispatched in
+    if (tid == 0) sh.misc[0] = atomicAdd(a.ticket, 1u);
 #pragma unroll
-    for (int i = tid; i < WARPS * RADIX; i += THREADS) warp_hist[i] = 0;
+    for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
     __syncthreads();
-#pragma unroll
-    for (int i = 0; i < ITEMS; ++i)
-        rank[i] = ballot_rank<false>(Tr::digit(e[i], pass, a.prm), full || wbase + i * 32 < tile_n, my_hist, lane, lane_lt);
-    __syncthreads();
-    if (tid < RADIX) column_bases<WARPS>(warp_hist, tid, excl);
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < ITEMS; ++i)
-        if (full || wbase + i * 32 < tile_n) tile_s[rank[i] + my_hist[Tr::digit(e[i], pass, a.prm)]] = e[i];
-    __syncthreads();
-#pragma unroll
-    for (int j = 0; j < ITEMS; ++j) {
-        const uint32_t idx = (uint32_t)j * THREADS + tid;
-        if (full || idx < tile_n) {
-            E v = tile_s[idx];
-            const unsigned d = Tr::digit(v, pass, a.prm);
-            if (pp.xf_out) v = Tr::xform_out(v, a.prm);
-            dst[goff[d] + (long long)idx] = v;
-        }
-    }
+    const uint32_t tile = sh.misc[0];
+    const uint32_t tile_n = min((uint32_t)TILE, a.portion_n - tile * (uint32_t)TILE);
+    if (tile_n == (uint32_t)TILE)
+        pass_tile<Tr, THREADS, ITEMS, true>(smem_raw, a, pp, src, dst, tile, tile_n);
+    else
+        pass_tile<Tr, THREADS, ITEMS, false>(smem_raw, a, pp, src, dst, tile, tile_n);
 }
 
 // ---------------------------------------------------------------------------
