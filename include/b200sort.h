@@ -105,9 +105,12 @@ int b200sort_records_host(void *recs, size_t n, size_t rec_bytes, size_t key_off
  * (memset nodes not counted).  bench.py reports the delta as gpu_launches. */
 unsigned long long b200sort_launch_count(void);
 
-/* Kernel-tuning override for sweeps: variant index per key width (bytes).
- * -1 restores the default.  Returns B200SORT_ERR_INVALID_ARG if unknown. */
+/* Kernel-tuning override for sweeps: K3 variant index per element width.
+ * key_bytes = 1, 2, 4, 8, 16 selects the key-only table of that width, 108 / 116
+ * the tables of 8- / 16-byte records.  -1 restores the default.  Returns
+ * B200SORT_ERR_INVALID_ARG if unknown.  b200sort_num_variants: size of a table. */
 int b200sort_set_variant(int key_bytes, int variant);
+int b200sort_num_variants(int key_bytes);
 
 /* Per-phase timing of one device sort, measured with CUDA events on `stream`
  * (synchronises!).  out_ms[0] = K1 histogram, out_ms[1] = K2 scan,

@@ -7,6 +7,7 @@ from __future__ import annotations
 
 import hashlib
 import os
+import re
 import shutil
 import subprocess
 import sys
@@ -17,13 +18,12 @@ CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libb200sort.so")
 STAMP = os.path.join(PKG, ".libb200sort.stamp")
 
-SOURCES = ["b200sort_api.cu", "aux_kernels.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC",
-    "--threads", "0",
 ]
+FAMILIES = {"KEYS": 0, "RECORDS": 1, "PARTITION": 2}
 
 
 def _nvcc() -> str:
@@ -53,32 +53,57 @@ def needs_build() -> bool:
         return fh.read().strip() != _fingerprint()
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile every .cu under csrc/ into libb200sort.so.  Returns its path."""
+def translation_units():
+    """(object name, source, extra -D flags) of every translation unit.  The K3
+    variants are compiled one kernel per unit (csrc/sort_impl.cuh names how many
+    each (family, width) table holds) so that the build parallelises."""
+    units = [("api", "b200sort_api.cu", []), ("aux", "aux_kernels.cu", [])]
+    text = open(os.path.join(CSRC, "sort_impl.cuh")).read()
+    for fam, w, nv in re.findall(r"#define B200_NV_([A-Z]+)_(\d+) (\d+)", text):
+        d = [f"-DB200_FAM={FAMILIES[fam]}", f"-DB200_W={w}"]
+        units.append((f"front_{fam.lower()}_{w}", "inst_front.cu", d))
+        for v in range(int(nv)):
+            units.append((f"k3_{fam.lower()}_{w}_v{v}", "inst_variant.cu", d + [f"-DB200_V={v}"]))
+    return units
+
+
+def build(force: bool = False, verbose: bool = False, jobs: int | None = None) -> str:
+    """Compile csrc/ into libb200sort.so (sm_100a only).  Returns its path."""
     if not force and not needs_build():
         return LIB
     nvcc = _nvcc()
-    objs = []
-    procs = []
-    for src in SOURCES:
-        obj = os.path.join(PKG, src.replace(".cu", ".o"))
-        cmd = [nvcc, *NVCC_FLAGS, "-I", os.path.join(ROOT, "include"), "-c",
-               os.path.join(CSRC, src), "-o", obj]
+    objdir = os.path.join(PKG, "build")
+    os.makedirs(objdir, exist_ok=True)
+    jobs = jobs or int(os.environ.get("B200SORT_BUILD_JOBS", "0")) or max(1, len(os.sched_getaffinity(0)))
+    units = translation_units()
+    # the heavy units (many unrolled items) first, so the tail of the build is short
+    units.sort(key=lambda u: (not u[0].startswith("k3_"), u[0]))
+    log = []
+
+    def compile_one(unit):
+        name, src, defs = unit
+        obj = os.path.join(objdir, name + ".o")
+        cmd = [nvcc, *NVCC_FLAGS, *defs, "-I", os.path.join(ROOT, "include"), "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
-            print(" ".join(cmd), file=sys.stderr)
-        procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
-        objs.append(obj)
-    for src, p in procs:
-        out, _ = p.communicate()
-        if verbose or p.returncode:
-            sys.stderr.write(out)
-        if p.returncode:
-            raise RuntimeError(f"nvcc failed on {src} (exit {p.returncode})")
-    link = [nvcc, "-shared", "-o", LIB, *objs]
-    subprocess.run(link, check=True)
-    for o in objs:
-        os.remove(o)
+        p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        return name, obj, p.returncode, p.stdout
+
+    from concurrent.futures import ThreadPoolExecutor
+    objs = []
+    with ThreadPoolExecutor(max_workers=jobs) as ex:
+        for name, obj, rc, out in ex.map(compile_one, units):
+            if verbose:
+                log.append(f"==== {name}\n{out}")
+            if rc:
+                sys.stderr.write(out)
+                raise RuntimeError(f"nvcc failed on {name} (exit {rc})")
+            objs.append(obj)
+    if verbose:
+        with open(os.path.join(objdir, "ptxas.log"), "w") as fh:
+            fh.write("\n".join(log))
+    subprocess.run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs], check=True)
+    shutil.rmtree(objdir, ignore_errors=not verbose) if not verbose else None
     with open(STAMP, "w") as fh:
         fh.write(_fingerprint())
     return LIB

@@ -26,6 +26,7 @@ PROTOTYPES = {
     "b200sort_records_host": (c_int, [c_void_p, c_size_t, c_size_t, c_size_t, c_int]),
     "b200sort_launch_count": (c_ulonglong, []),
     "b200sort_set_variant": (c_int, [c_int, c_int]),
+    "b200sort_num_variants": (c_int, [c_int]),
     "b200sort_keys_device_timed": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_int, c_void_p, c_uint,
                                            POINTER(c_float), c_int]),
     "b200sort_generate": (c_int, [c_void_p, c_size_t, c_int, c_int, c_double, c_uint64, c_uint64, c_void_p]),

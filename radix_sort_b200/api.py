@@ -197,7 +197,13 @@ def launch_count() -> int:
 
 
 def set_variant(key_bytes_: int, variant: int) -> None:
+    """Select K3 variant `variant` (-1 = default) for keys of key_bytes_ bytes
+    (108 / 116: 8- / 16-byte records).  Tuning sweeps only."""
     check(_ffi.lib().b200sort_set_variant(key_bytes_, variant))
+
+
+def num_variants(key_bytes_: int) -> int:
+    return int(_ffi.lib().b200sort_num_variants(key_bytes_))
 
 
 def sort_timed(data, kind=None, *, workspace=None, flags: int = 0):

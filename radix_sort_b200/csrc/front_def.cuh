@@ -1,0 +1,182 @@
+// front_def.cuh -- definition of sort_front<FAM, W>: the launch sequence of one
+// sort (replaces the body of RadixSort::radix_sort, reference mod.rs:61-176).
+// Included only by inst_front.cu, which instantiates it for one (family, width).
+// There is deliberately no CPU path: every call launches the sm_100a kernels or
+// returns an error.
+#pragma once
+#include "sort_impl.cuh"
+
+namespace b200 {
+
+template <int FAM, int W, int I = 0>
+cudaError_t launch_pass_idx(int variant, const PassArgs<typename FamilyTraits<FAM, W>::type>& a, cudaStream_t st) {
+    if constexpr (I >= num_variants<FAM, W>()) {
+        return cudaErrorInvalidValue;
+    } else {
+        if (variant == I) return VariantEntry<FAM, W, I>::launch(a, st);
+        return launch_pass_idx<FAM, W, I + 1>(variant, a, st);
+    }
+}
+
+template <int FAM, int W>
+size_t temp_bytes_front(size_t n) {
+    using Tr = typename FamilyTraits<FAM, W>::type;
+    // the maximum over all variants, so a sweep never outgrows the workspace
+    size_t m = 0;
+    for (int i = 0; i < num_variants<FAM, W>(); ++i) {
+        const VariantDesc d = Variants<FAM, W>::v[i];
+        const size_t t = make_layout(n ? n : 1, W, Tr::DIGITS, d.threads * d.items).total;
+        if (t > m) m = t;
+    }
+    return m;
+}
+
+template <int FAM, int W>
+int make_params(const SortCall& c, typename FamilyTraits<FAM, W>::type::Params* prm) {
+    using Tr = typename FamilyTraits<FAM, W>::type;
+    typename Tr::Params p{};
+    if constexpr (FAM == FAM_KEYS) {
+        p.xf = c.xf;
+    } else if constexpr (FAM == FAM_RECORDS) {
+        p.key_shift = c.key_shift;
+        p.xf = c.xf;
+    } else {
+        using U = typename Tr::elem_t;
+        p.nsplit = c.nsplit;
+        p.xf = c.xf;
+        const U* raw = static_cast<const U*>(c.splitters);
+        for (int j = 0; j < c.nsplit; ++j) p.spl[j] = to_ordered_rt<U>(raw[j], c.xf);
+        for (int j = 1; j < c.nsplit; ++j)
+            if (ordered_less<U>(p.spl[j], p.spl[j - 1])) return fail(B200SORT_ERR_INVALID_ARG, "splitters are not ascending");
+    }
+    *prm = p;
+    return B200SORT_OK;
+}
+
+template <int FAM, int W>
+int sort_front(const SortCall& c) {
+    using Tr = typename FamilyTraits<FAM, W>::type;
+    using E = typename Tr::elem_t;
+    static_assert(sizeof(E) == W, "element width");
+    constexpr int D = Tr::DIGITS;
+    const size_t n = c.n;
+    cudaStream_t st = c.st;
+    typename Tr::Params prm;
+    if (int rc = make_params<FAM, W>(c, &prm)) return rc;
+    if (n == 0) {
+        if (c.hist_copy) B200_CU(cudaMemsetAsync(c.hist_copy, 0, (size_t)c.hist_copy_words * 8, st));
+        return B200SORT_OK;
+    }
+    E* d_elems = static_cast<E*>(c.elems);
+    if (!d_elems || !c.ws) return fail(B200SORT_ERR_INVALID_ARG, "null device pointer");
+    if (((uintptr_t)d_elems % alignof(E)) != 0 || (c.alt_out && ((uintptr_t)c.alt_out % alignof(E)) != 0))
+        return fail(B200SORT_ERR_INVALID_ARG, "keys not aligned to the element size");
+    if (((uintptr_t)c.ws % 256) != 0) return fail(B200SORT_ERR_INVALID_ARG, "workspace not 256-byte aligned");
+
+    int variant = variant_override(FAM, W);
+    if (variant < 0 || variant >= num_variants<FAM, W>()) variant = 0;
+    // the TMA ring of the persistent kernel needs 16-byte aligned tiles
+    const bool aligned16 = ((uintptr_t)d_elems % 16) == 0 && (!c.alt_out || ((uintptr_t)c.alt_out % 16) == 0);
+    if (Variants<FAM, W>::v[variant].kernel == 1 && !aligned16) variant = Variants<FAM, W>::FALLBACK;
+    const VariantDesc vd = Variants<FAM, W>::v[variant];
+    const int tile = vd.threads * vd.items;
+    const Layout L = make_layout(n, W, D, tile);
+    if (c.ws_bytes < L.total) return fail(B200SORT_ERR_INVALID_ARG, "workspace smaller than b200sort_temp_bytes()");
+
+    unsigned char* ws = static_cast<unsigned char*>(c.ws);
+    // alt_out: single-pass callers (the multi-GPU partition) name the destination
+    // themselves; the result stays there and nothing is copied back
+    E* tmp = c.alt_out ? static_cast<E*>(c.alt_out) : reinterpret_cast<E*>(ws + L.tmp_off);
+    unsigned long long* bins = reinterpret_cast<unsigned long long*>(ws + L.bins_off);
+    Plan* plan = reinterpret_cast<Plan*>(ws + L.plan_off);
+    unsigned long long* hist = reinterpret_cast<unsigned long long*>(ws + L.hist_off);
+    uint32_t* tickets = reinterpret_cast<uint32_t*>(ws + L.ticket_off);
+    uint32_t* lookback = reinterpret_cast<uint32_t*>(ws + L.lb_off);
+    uint32_t* stats = reinterpret_cast<uint32_t*>(ws + L.stats_off);
+
+    PhaseTimer timer(c.out_ms != nullptr, st);
+    timer.mark();
+    B200_CU(cudaMemsetAsync(ws + L.zero_off, 0, L.zero_bytes, st));
+
+    // K1: one read, all digit histograms
+    {
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        constexpr int HT = 512;
+        constexpr size_t HS = HistCfg<Tr>::SMEM;
+        auto hk = hist_all_digits_kernel<Tr, HT>;
+        static std::atomic<unsigned> configured{0};  // bit per device
+        if (HS > 48 * 1024 && !(configured.load(std::memory_order_acquire) & (1u << (dev & 31)))) {
+            B200_CU(cudaFuncSetAttribute(hk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HS));
+            configured.fetch_or(1u << (dev & 31), std::memory_order_release);
+        }
+        const size_t per_sm = std::max<size_t>(1, std::min<size_t>(4, (220 * 1024) / HS));
+        const size_t vecs = (n * W + 15) / 16;
+        size_t blocks = (vecs + (size_t)HT * 4 - 1) / ((size_t)HT * 4);
+        const size_t cap = (size_t)sms * per_sm;
+        if (blocks > cap) blocks = cap;
+        if (blocks < 1) blocks = 1;
+        hk<<<(unsigned)blocks, HT, HS, st>>>(d_elems, n, hist, prm);
+        count_launch();
+        B200_CU(cudaGetLastError());
+    }
+    timer.mark();
+    if (c.hist_copy)
+        B200_CU(cudaMemcpyAsync(c.hist_copy, hist, (size_t)c.hist_copy_words * 8, cudaMemcpyDeviceToDevice, st));
+    // K2: bucket bases + pass plan
+    scan_plan_kernel<<<1, RADIX, 0, st>>>(hist, bins, plan, (unsigned long long)n, D, L.portions,
+                                          (c.flags & B200SORT_FLAG_NO_SKIP) ? 1 : 0);
+    count_launch();
+    B200_CU(cudaGetLastError());
+    timer.mark();
+
+    // K3: one launch per digit per portion
+    size_t lb_cursor = 0;
+    for (int p = 0; p < D; ++p) {
+        for (int q = 0; q < L.portions; ++q) {
+            const size_t off = (size_t)q * L.portion_elems;
+            const size_t pn = (q + 1 < L.portions) ? L.portion_elems : n - off;
+            PassArgs<Tr> a;
+            a.keys = d_elems;
+            a.tmp = tmp;
+            a.plan = plan;
+            a.pass = p;
+            a.portion_off = off;
+            a.portion_n = (uint32_t)pn;
+            a.num_tiles = (uint32_t)((pn + tile - 1) / tile);
+            a.grid = a.num_tiles;
+            a.bins_in = bins + ((size_t)p * L.portions + q) * RADIX;
+            a.bins_out = (q + 1 < L.portions) ? bins + ((size_t)p * L.portions + q + 1) * RADIX : nullptr;
+            a.lookback = lookback + lb_cursor * RADIX;
+            a.ticket = tickets + (size_t)p * L.portions + q;
+            a.stats = stats;
+            a.prm = prm;
+            lb_cursor += a.num_tiles;
+            B200_CU((launch_pass_idx<FAM, W>(variant, a, st)));
+        }
+        timer.mark();
+    }
+    // result in tmp after an odd number of executed passes (mod.rs:170-174)
+    if (!c.alt_out) {
+        const size_t bytes = n * W;
+        size_t blocks = (bytes / 16 + 255) / 256;
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        if (blocks < 1) blocks = 1;
+        copy_back_kernel<E><<<(unsigned)blocks, 256, 0, st>>>(d_elems, tmp, n, plan);
+        count_launch();
+        B200_CU(cudaGetLastError());
+    }
+    timer.mark();
+
+    if (c.out_ms) {
+        if (c.out_len < D + 4) return fail(B200SORT_ERR_INVALID_ARG, "out_len < digits + 4");
+        B200_CU(cudaStreamSynchronize(st));
+        // marks: 0 start | 1 after memset+K1 | 2 after K2 | 3..2+D after each pass | 3+D after copy-back
+        for (int i = 0; i < D + 3; ++i) cudaEventElapsedTime(&c.out_ms[i], timer.ev[i], timer.ev[i + 1]);
+        cudaEventElapsedTime(&c.out_ms[D + 3], timer.ev.front(), timer.ev.back());
+    }
+    return B200SORT_OK;
+}
+
+}  // namespace b200

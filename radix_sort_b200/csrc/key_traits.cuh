@@ -107,6 +107,37 @@ __host__ __device__ __forceinline__ bool prefix_less<u128>(u128 a, u128 b, int p
     return ah < bh || (ah == bh && a.lo < b.lo);
 }
 
+// ---- run-time transform selection ---------------------------------------------
+// The sort kernels take the transform as a launch parameter (xf) instead of a
+// template parameter: it is applied only on the first load and the last store
+// of a sort, and one kernel image per key WIDTH keeps the library small.
+template <typename U>
+__host__ __device__ __forceinline__ U to_ordered_rt(U k, int xf) {
+    constexpr int BITS = (int)sizeof(U) * 8;
+    constexpr U SIGN = (U)((U)1 << (BITS - 1));
+    U m = (xf == XF_NONE) ? (U)0 : SIGN;
+    if (xf == XF_FLOAT && (k & SIGN)) m = (U)~(U)0;
+    return (U)(k ^ m);
+}
+template <typename U>
+__host__ __device__ __forceinline__ U from_ordered_rt(U t, int xf) {
+    constexpr int BITS = (int)sizeof(U) * 8;
+    constexpr U SIGN = (U)((U)1 << (BITS - 1));
+    U m = (xf == XF_NONE) ? (U)0 : SIGN;
+    if (xf == XF_FLOAT && !(t & SIGN)) m = (U)~(U)0;
+    return (U)(t ^ m);
+}
+template <>
+__host__ __device__ __forceinline__ u128 to_ordered_rt<u128>(u128 k, int xf) {
+    if (xf != XF_NONE) k.hi ^= 0x8000000000000000ull;  // no 128-bit float kind exists
+    return k;
+}
+template <>
+__host__ __device__ __forceinline__ u128 from_ordered_rt<u128>(u128 k, int xf) {
+    if (xf != XF_NONE) k.hi ^= 0x8000000000000000ull;
+    return k;
+}
+
 // splitmix64 finaliser: the mixing function of the counter-based generators
 // and of the multiset fingerprint.
 __host__ __device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
@@ -117,20 +148,19 @@ __host__ __device__ __forceinline__ unsigned long long mix64(unsigned long long 
 }
 
 // Key-only element traits: the element moved by the passes IS the key.
-template <typename U, int XF_>
+template <typename U>
 struct KeyTraits {
     using elem_t = U;
     using key_t = U;
-    static constexpr int XF = XF_;
     static constexpr int KEY_BYTES = (int)sizeof(U);
     static constexpr int DIGITS = (int)sizeof(U);  // NUMBER_OF_DIGITS, radix_digits.rs:8..117
     // equal keys are bit-identical, so a pass only has to keep same-digit keys in
     // the order of their lower digits -- which K3 can check exactly (sort_kernels.cuh)
     static constexpr bool NEEDS_STABLE = false;
-    struct Params {};
+    struct Params { int xf; };
     __device__ __forceinline__ static bool prefix_less(elem_t a, elem_t b, int pass, const Params&) { return b200::prefix_less<U>(a, b, pass); }
-    __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params&) { return to_ordered<U, XF_>(e); }
-    __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params&) { return from_ordered<U, XF_>(e); }
+    __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params& p) { return to_ordered_rt<U>(e, p.xf); }
+    __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params& p) { return from_ordered_rt<U>(e, p.xf); }
     __device__ __forceinline__ static unsigned digit(elem_t e, int pass, const Params&) { return digit_of<U>(e, pass); }
 };
 
@@ -138,23 +168,23 @@ struct KeyTraits {
 // destination rank of the key, r = #{j : splitter[j] <= ordered(key)}.  Keys are
 // moved raw; splitters are held in the ordered domain.
 constexpr int MAX_SPLITTERS = 15;
-template <typename U, int XF_>
+template <typename U>
 struct PartitionTraits {
     using elem_t = U;
     using key_t = U;
-    static constexpr int XF = XF_;
     static constexpr int KEY_BYTES = (int)sizeof(U);
     static constexpr int DIGITS = 1;
     static constexpr bool NEEDS_STABLE = false;  // order inside a destination is irrelevant: it is sorted next
     struct Params {
         U spl[MAX_SPLITTERS];
         int nsplit;
+        int xf;
     };
     __device__ __forceinline__ static bool prefix_less(elem_t, elem_t, int, const Params&) { return false; }
     __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params&) { return e; }
     __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params&) { return e; }
     __device__ __forceinline__ static unsigned digit(elem_t e, int, const Params& p) {
-        const U k = to_ordered<U, XF_>(e);
+        const U k = to_ordered_rt<U>(e, p.xf);
         unsigned r = 0;
 #pragma unroll
         for (int j = 0; j < MAX_SPLITTERS; ++j)
@@ -166,17 +196,16 @@ struct PartitionTraits {
 // Record traits: `(K, V)` tuples moved whole, key = one field of the record
 // (radix_digits.rs:126-136).  R = unsigned type as wide as the record (8 or 16
 // bytes), K = unsigned type of the key, key_shift = 8 * byte offset of the key.
-template <typename R, typename K, int XF_> struct RecordTraits;
+template <typename R, typename K> struct RecordTraits;
 
-template <typename K, int XF_>
-struct RecordTraits<unsigned long long, K, XF_> {  // 8-byte record, 4-byte key
+template <typename K>
+struct RecordTraits<unsigned long long, K> {  // 8-byte record, 4-byte key
     using elem_t = unsigned long long;
     using key_t = K;
-    static constexpr int XF = XF_;
     static constexpr int KEY_BYTES = (int)sizeof(K);
     static constexpr int DIGITS = (int)sizeof(K);
     static constexpr bool NEEDS_STABLE = true;  // payloads make the order of equal keys observable (tests.rs:175-187)
-    struct Params { int key_shift; };
+    struct Params { int key_shift; int xf; };
     __device__ __forceinline__ static bool prefix_less(elem_t, elem_t, int, const Params&) { return false; }
     __device__ __forceinline__ static K key(elem_t e, const Params& p) { return (K)(e >> p.key_shift); }
     __device__ __forceinline__ static elem_t with_key(elem_t e, K k, const Params& p) {
@@ -184,25 +213,24 @@ struct RecordTraits<unsigned long long, K, XF_> {  // 8-byte record, 4-byte key
         return (e & ~mask) | ((elem_t)k << p.key_shift);
     }
     __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params& p) {
-        return with_key(e, to_ordered<K, XF_>(key(e, p)), p);
+        return with_key(e, to_ordered_rt<K>(key(e, p), p.xf), p);
     }
     __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params& p) {
-        return with_key(e, from_ordered<K, XF_>(key(e, p)), p);
+        return with_key(e, from_ordered_rt<K>(key(e, p), p.xf), p);
     }
     __device__ __forceinline__ static unsigned digit(elem_t e, int pass, const Params& p) {
         return (unsigned)(e >> (p.key_shift + 8 * pass)) & 0xFFu;
     }
 };
 
-template <int XF_>
-struct RecordTraits<u128, unsigned long long, XF_> {  // 16-byte record, 8-byte key
+template <>
+struct RecordTraits<u128, unsigned long long> {  // 16-byte record, 8-byte key
     using elem_t = u128;
     using key_t = unsigned long long;
-    static constexpr int XF = XF_;
     static constexpr int KEY_BYTES = 8;
     static constexpr int DIGITS = 8;
     static constexpr bool NEEDS_STABLE = true;
-    struct Params { int key_shift; };  // 0 -> key in .lo, 64 -> key in .hi
+    struct Params { int key_shift; int xf; };  // key_shift: 0 -> key in .lo, 64 -> key in .hi
     __device__ __forceinline__ static bool prefix_less(elem_t, elem_t, int, const Params&) { return false; }
     __device__ __forceinline__ static key_t key(elem_t e, const Params& p) { return p.key_shift ? e.hi : e.lo; }
     __device__ __forceinline__ static elem_t with_key(elem_t e, key_t k, const Params& p) {
@@ -210,10 +238,10 @@ struct RecordTraits<u128, unsigned long long, XF_> {  // 16-byte record, 8-byte 
         return e;
     }
     __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params& p) {
-        return with_key(e, to_ordered<key_t, XF_>(key(e, p)), p);
+        return with_key(e, to_ordered_rt<key_t>(key(e, p), p.xf), p);
     }
     __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params& p) {
-        return with_key(e, from_ordered<key_t, XF_>(key(e, p)), p);
+        return with_key(e, from_ordered_rt<key_t>(key(e, p), p.xf), p);
     }
     __device__ __forceinline__ static unsigned digit(elem_t e, int pass, const Params& p) {
         return (unsigned)(key(e, p) >> (8 * pass)) & 0xFFu;

@@ -143,7 +143,7 @@ hist_all_digits_kernel(const typename Tr::elem_t* __restrict__ in, size_t n,
 // transform is applied, where the result ends up).
 // bins layout: [digit][portion][256].
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(RADIX)
+static __global__ void __launch_bounds__(RADIX)
 scan_plan_kernel(const unsigned long long* __restrict__ hist, unsigned long long* __restrict__ bins,
                  Plan* __restrict__ plan, unsigned long long n, int digits, int portions, int no_skip) {
     __shared__ unsigned long long warp_tot[RADIX / 32];
@@ -208,6 +208,24 @@ scan_plan_kernel(const unsigned long long* __restrict__ hist, unsigned long long
 //   * records (NEEDS_STABLE) always rank with ballots: 8 ballots give the lanes
 //     holding the same digit, rank = leader's counter + lower lanes of the group,
 //     lane-ordered by construction.
+//
+// Look-back.  With C tiles in flight and a tile started every g = T_tile / C, a
+// walk that pays one L2 round trip l per predecessor settles at a depth of about
+// l / g predecessors -- i.e. l^2 C / T_tile of pure latency per tile, which was as
+// long as the rest of the tile (r01 ncu: the spin loop held 45 % of the stall
+// samples).  So the walk reads LB_BATCH predecessors per round trip (independent
+// relaxed loads), and the first batch is requested before the scatter so that it
+// has landed by the time the scatter is done.
+//
+// Two kernels share this tile code:
+//   onesweep_pass_kernel        one tile per CTA, keys loaded straight into
+//                               registers; any alignment; the general path.
+//   onesweep_persistent_kernel  CTAs stay resident and draw tiles from the ticket
+//                               counter; tile i+1 is fetched by a TMA bulk copy
+//                               (cp.async.bulk, completion on an mbarrier) into
+//                               the other half of a two-tile ring while tile i is
+//                               ranked; the ring slot doubles as the digit-sorted
+//                               staging buffer.  Needs 16-byte aligned buffers.
 // ---------------------------------------------------------------------------
 template <typename Tr>
 struct PassArgs {
@@ -218,6 +236,7 @@ struct PassArgs {
     unsigned long long portion_off;      // first element of this portion
     uint32_t portion_n;                  // elements in this portion
     uint32_t num_tiles;
+    uint32_t grid;                       // CTAs to launch (persistent kernel: resident CTAs)
     const unsigned long long* bins_in;   // [256] global base of each bucket for this portion
     unsigned long long* bins_out;        // [256] base for the next portion (or null)
     uint32_t* lookback;                  // [num_tiles][256] status words, zeroed
@@ -225,6 +244,8 @@ struct PassArgs {
     uint32_t* stats;                     // [0] tiles that took the re-rank fallback
     typename Tr::Params prm;
 };
+
+constexpr int LB_BATCH = 8;
 
 template <typename Tr, int THREADS, int ITEMS>
 struct PassSmem {
@@ -235,10 +256,12 @@ struct PassSmem {
     static constexpr size_t GPTR_BYTES = (size_t)RADIX * sizeof(unsigned long long);
     static constexpr size_t EXCL_BYTES = (size_t)RADIX * sizeof(uint32_t);
     static constexpr size_t CNT_BYTES = (size_t)RADIX * sizeof(uint32_t);
-    static constexpr size_t TOTAL = TILE_BYTES + HIST_BYTES + GPTR_BYTES + EXCL_BYTES + CNT_BYTES + 64;
+    static constexpr size_t AUX_BYTES = HIST_BYTES + GPTR_BYTES + EXCL_BYTES + CNT_BYTES + 64 + 16;
+    static constexpr size_t TOTAL = TILE_BYTES + AUX_BYTES;             // one-tile kernel
+    static constexpr size_t TOTAL_PERSISTENT = 2 * TILE_BYTES + AUX_BYTES;  // two-tile ring
 };
 
-// views into the dynamic shared memory of one CTA
+// views into the dynamic shared memory of one CTA: [tile buffers | aux]
 template <typename Tr, int THREADS, int ITEMS>
 struct PassShared {
     using SM = PassSmem<Tr, THREADS, ITEMS>;
@@ -247,14 +270,17 @@ struct PassShared {
     unsigned long long* gptr;       // [256] byte address in dst of slot 0 of the tile, per digit
     uint32_t* excl;                 // [256] keys of the tile with a smaller digit
     uint32_t* cnt;                  // [256] keys of the tile with this digit
-    uint32_t* misc;                 // [0] ticket, [1..8] warp totals of the digit scan
-    __device__ __forceinline__ explicit PassShared(unsigned char* raw) {
+    uint32_t* misc;                 // [0..1] tickets, [2..9] warp totals of the digit scan
+    unsigned long long* mbar;       // [2] mbarriers of the ring (persistent kernel)
+    __device__ __forceinline__ PassShared(unsigned char* raw, size_t tile_bytes_total) {
         tile = reinterpret_cast<typename Tr::elem_t*>(raw);
-        warp_hist = reinterpret_cast<uint32_t*>(raw + SM::TILE_BYTES);
-        gptr = reinterpret_cast<unsigned long long*>(raw + SM::TILE_BYTES + SM::HIST_BYTES);
-        excl = reinterpret_cast<uint32_t*>(raw + SM::TILE_BYTES + SM::HIST_BYTES + SM::GPTR_BYTES);
+        unsigned char* aux = raw + tile_bytes_total;
+        warp_hist = reinterpret_cast<uint32_t*>(aux);
+        gptr = reinterpret_cast<unsigned long long*>(aux + SM::HIST_BYTES);
+        excl = reinterpret_cast<uint32_t*>(aux + SM::HIST_BYTES + SM::GPTR_BYTES);
         cnt = excl + RADIX;
         misc = cnt + RADIX;
+        mbar = reinterpret_cast<unsigned long long*>(misc + 16);
     }
 };
 
@@ -294,10 +320,42 @@ __device__ __forceinline__ void column_bases(uint32_t* warp_hist, int d, uint32_
     }
 }
 
+// Decoupled look-back for one digit, LB_BATCH predecessors per round trip.
+// p points at the status word of tile `pos` (the nearest predecessor) for this
+// digit; tiles below 0 read as {INCLUSIVE, 0}.
+struct LookBack {
+    uint32_t v[LB_BATCH];
+    __device__ __forceinline__ void request(const uint32_t* p, int pos) {
+#pragma unroll
+        for (int j = 0; j < LB_BATCH; ++j)
+            v[j] = (pos - j >= 0) ? ld_relaxed_u32(p - (size_t)j * RADIX) : LB_FLAG_INCLUSIVE;
+    }
+    // sum of the counts of all preceding tiles
+    __device__ __forceinline__ uint32_t resolve(const uint32_t* p, int pos) {
+        uint32_t sum = 0;
+        for (;;) {
+            bool done = false;
+#pragma unroll
+            for (int j = 0; j < LB_BATCH; ++j) {
+                if (!done) {
+                    uint32_t x = v[j];
+                    while ((x & (LB_FLAG_PARTIAL | LB_FLAG_INCLUSIVE)) == 0) x = ld_relaxed_u32(p - (size_t)j * RADIX);
+                    sum += x & LB_VALUE_MASK;
+                    done = (x & LB_FLAG_INCLUSIVE) != 0;
+                }
+            }
+            if (done) return sum;
+            p -= (size_t)LB_BATCH * RADIX;
+            pos -= LB_BATCH;
+            request(p, pos);
+        }
+    }
+};
+
 // coalesced run write-out of the digit-sorted tile; VERIFY adds the order check
 template <typename Tr, int THREADS, int ITEMS, bool FULL, bool VERIFY>
 __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& sh, const PassArgs<Tr>& a,
-                                          const PassPlan& pp, uint32_t tile_n, int tid) {
+                                          uint32_t xf_out, uint32_t tile_n, int tid) {
     using E = typename Tr::elem_t;
     bool bad = false;
 #pragma unroll
@@ -308,7 +366,7 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
             if (VERIFY && (idx + 1 < (FULL ? (uint32_t)(THREADS * ITEMS) : tile_n)))
                 bad |= Tr::prefix_less(sh.tile[idx + 1], v, a.pass, a.prm);
             const unsigned d = Tr::digit(v, a.pass, a.prm);
-            if (pp.xf_out) v = Tr::xform_out(v, a.prm);
+            if (xf_out) v = Tr::xform_out(v, a.prm);
             *reinterpret_cast<E*>(sh.gptr[d] + (unsigned long long)idx * sizeof(E)) = v;
         }
     }
@@ -319,16 +377,19 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
 // construction) from the keys still in global memory, and rewrite its slots.
 // Entered by a whole CTA; warp_hist may hold anything; excl/gptr are valid.
 template <typename Tr, int THREADS, int ITEMS>
-__device__ __noinline__ void rerank_tile(unsigned char* raw, const PassArgs<Tr>* ap, const typename Tr::elem_t* src_tile,
+__device__ __noinline__ void rerank_tile(typename Tr::elem_t* tile_buf, unsigned char* aux_minus_tiles, size_t tile_bytes_total,
+                                         const PassArgs<Tr>* ap, const typename Tr::elem_t* src_tile,
                                          uint32_t tile_n, uint32_t xf_in, uint32_t xf_out) {
     using E = typename Tr::elem_t;
     constexpr int WARPS = THREADS / 32;
     const PassArgs<Tr>& a = *ap;
-    PassShared<Tr, THREADS, ITEMS> sh(raw);
+    PassShared<Tr, THREADS, ITEMS> sh(aux_minus_tiles, tile_bytes_total);
+    sh.tile = tile_buf;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lane_lt = (1u << lane) - 1u;
     const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
     uint32_t* my_hist = sh.warp_hist + warp * RADIX;
+    __syncthreads();
     for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
     __syncthreads();
     E e[ITEMS];
@@ -349,33 +410,30 @@ __device__ __noinline__ void rerank_tile(unsigned char* raw, const PassArgs<Tr>*
     for (int i = 0; i < ITEMS; ++i)
         if (wbase + i * 32 < tile_n) sh.tile[rank[i] + my_hist[Tr::digit(e[i], a.pass, a.prm)]] = e[i];
     __syncthreads();
-    PassPlan pp;
-    pp.skip = 0; pp.src_is_tmp = 0; pp.xf_in = xf_in; pp.xf_out = xf_out;
-    write_out<Tr, THREADS, ITEMS, false, false>(sh, a, pp, tile_n, tid);
+    write_out<Tr, THREADS, ITEMS, false, false>(sh, a, xf_out, tile_n, tid);
+    __syncthreads();
 }
 
-// One tile, FULL (all THREADS*ITEMS slots valid) known at compile time so the
-// per-key loops carry no bounds predicates.
-template <typename Tr, int THREADS, int ITEMS, bool FULL>
-__device__ __forceinline__ void pass_tile(unsigned char* raw, const PassArgs<Tr>& a, const PassPlan& pp,
-                                          const typename Tr::elem_t* __restrict__ src, typename Tr::elem_t* __restrict__ dst,
-                                          uint32_t tile, uint32_t tile_n) {
+// One tile whose keys are already in registers (warp-striped: item i of lane l =
+// element i*32+l of the warp's contiguous segment, so slot order == memory order).
+// FULL (all THREADS*ITEMS slots valid) is known at compile time so the per-key
+// loops carry no bounds predicates.  sh.tile may alias the buffer the keys were
+// read from: the first barrier below orders those reads before the scatter.
+// Returns true when the order check of the write-out failed (caller re-ranks).
+struct NoHook { __device__ __forceinline__ void operator()() const {} };
+
+template <typename Tr, int THREADS, int ITEMS, bool FULL, typename Hook>
+__device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, THREADS, ITEMS>& sh, const PassArgs<Tr>& a,
+                                                 const PassPlan& pp, typename Tr::elem_t (&e)[ITEMS],
+                                                 typename Tr::elem_t* __restrict__ dst, uint32_t tile, uint32_t tile_n,
+                                                 Hook after_count) {
     using E = typename Tr::elem_t;
     constexpr int WARPS = THREADS / 32;
-    constexpr int TILE = THREADS * ITEMS;
     constexpr int LB0 = THREADS - RADIX;  // the last 256 threads run the look-back
-    PassShared<Tr, THREADS, ITEMS> sh(raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int pass = a.pass;
     const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
-    const E* src_tile = src + (size_t)tile * TILE;
 
-    // ---- stage: warp-striped load (item i of lane l = element i*32+l of the
-    // warp's contiguous segment), so slot order == memory order
-    E e[ITEMS];
-#pragma unroll
-    for (int i = 0; i < ITEMS; ++i)
-        if (FULL || wbase + i * 32 < tile_n) e[i] = ld_elem(src_tile + wbase + i * 32);
     if (pp.xf_in) {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) e[i] = Tr::xform_in(e[i], a.prm);
@@ -396,6 +454,7 @@ __device__ __forceinline__ void pass_tile(unsigned char* raw, const PassArgs<Tr>
             if (FULL || wbase + i * 32 < tile_n) atomicAdd(&my_hist[Tr::digit(e[i], pass, a.prm)], 1u);
     }
     __syncthreads();
+    after_count();  // persistent kernel: thread 0 starts the bulk copy of the next tile
 
     // ---- 2. thread d owns digit d: tile count -> publish -> scan over digits ->
     // per-warp first slots inside the digit-sorted tile
@@ -405,18 +464,22 @@ __device__ __forceinline__ void pass_tile(unsigned char* raw, const PassArgs<Tr>
         count = column_total<WARPS>(sh.warp_hist, tid);
         st_relaxed_u32(lb + tid, (tile == 0 ? LB_FLAG_INCLUSIVE : LB_FLAG_PARTIAL) | count);
     }
+    // the look-back threads ask for the first batch of predecessors now; the
+    // answers arrive while the scan and the scatter run
+    LookBack look;
+    if (tid >= LB0) look.request(lb - RADIX + (tid - LB0), (int)tile - 1);
     uint32_t incl = count;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const uint32_t y = __shfl_up_sync(FULL_MASK, incl, o);
         if (lane >= o) incl += y;
     }
-    if (lane == 31 && warp < RADIX / 32) sh.misc[1 + warp] = incl;
+    if (lane == 31 && warp < RADIX / 32) sh.misc[2 + warp] = incl;
     __syncthreads();
     if (tid < RADIX) {
         uint32_t base = 0;
 #pragma unroll
-        for (int w = 0; w < RADIX / 32; ++w) base += (w < warp) ? sh.misc[1 + w] : 0u;
+        for (int w = 0; w < RADIX / 32; ++w) base += (w < warp) ? sh.misc[2 + w] : 0u;
         const uint32_t excl = base + incl - count;  // keys of the tile with a smaller digit
         sh.excl[tid] = excl;
         sh.cnt[tid] = count;
@@ -433,22 +496,13 @@ __device__ __forceinline__ void pass_tile(unsigned char* raw, const PassArgs<Tr>
             sh.tile[slot] = e[i];
         }
 
-    // ---- decoupled look-back, one digit per thread of the last 256 threads: sum
-    // the counts of preceding tiles until one that knows its inclusive prefix
+    // ---- decoupled look-back, one digit per thread of the last 256 threads
     if (tid >= LB0) {
         const int d = tid - LB0;
         const uint32_t cnt_d = sh.cnt[d];
         unsigned long long excl_tiles = 0;
         if (tile > 0) {
-            uint32_t sum = 0;
-            const uint32_t* q = lb + d;
-            for (;;) {
-                q -= RADIX;
-                uint32_t v;
-                do { v = ld_relaxed_u32(q); } while ((v & (LB_FLAG_PARTIAL | LB_FLAG_INCLUSIVE)) == 0);
-                sum += v & LB_VALUE_MASK;
-                if (v & LB_FLAG_INCLUSIVE) break;
-            }
+            const uint32_t sum = look.resolve(lb - RADIX + d, (int)tile - 1);
             st_relaxed_u32(lb + d, LB_FLAG_INCLUSIVE | (sum + cnt_d));
             excl_tiles = sum;
         }
@@ -460,19 +514,17 @@ __device__ __forceinline__ void pass_tile(unsigned char* raw, const PassArgs<Tr>
 
     // ---- coalesced run write-out; key-only passes check the order of the tile
     if (Tr::NEEDS_STABLE || pass == 0) {
-        write_out<Tr, THREADS, ITEMS, FULL, false>(sh, a, pp, tile_n, tid);
-        return;
+        write_out<Tr, THREADS, ITEMS, FULL, false>(sh, a, pp.xf_out, tile_n, tid);
+        return false;
     }
-    const bool bad = write_out<Tr, THREADS, ITEMS, FULL, true>(sh, a, pp, tile_n, tid);
-    if (!__syncthreads_or(bad)) return;
-    if (tid == 0) atomicAdd(a.stats, 1u);
-    rerank_tile<Tr, THREADS, ITEMS>(raw, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
+    return write_out<Tr, THREADS, ITEMS, FULL, true>(sh, a, pp.xf_out, tile_n, tid);
 }
 
 template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     using E = typename Tr::elem_t;
+    using SM = PassSmem<Tr, THREADS, ITEMS>;
     constexpr int WARPS = THREADS / 32;
     constexpr int TILE = THREADS * ITEMS;
     static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit needed");
@@ -480,9 +532,9 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     const PassPlan pp = a.plan->pass[a.pass];
     if (pp.skip) return;
 
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    PassShared<Tr, THREADS, ITEMS> sh(smem_raw);
-    const int tid = threadIdx.x;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    PassShared<Tr, THREADS, ITEMS> sh(smem_raw, SM::TILE_BYTES);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     const E* __restrict__ src = (pp.src_is_tmp ? a.tmp : a.keys) + a.portion_off;
     E* __restrict__ dst = pp.src_is_tmp ? a.keys : a.tmp;
@@ -495,10 +547,137 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     __syncthreads();
     const uint32_t tile = sh.misc[0];
     const uint32_t tile_n = min((uint32_t)TILE, a.portion_n - tile * (uint32_t)TILE);
-    if (tile_n == (uint32_t)TILE)
-        pass_tile<Tr, THREADS, ITEMS, true>(smem_raw, a, pp, src, dst, tile, tile_n);
-    else
-        pass_tile<Tr, THREADS, ITEMS, false>(smem_raw, a, pp, src, dst, tile, tile_n);
+    const E* src_tile = src + (size_t)tile * TILE;
+    const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
+    E e[ITEMS];
+    bool bad;
+    if (tile_n == (uint32_t)TILE) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) e[i] = ld_elem(src_tile + wbase + i * 32);
+        bad = rank_and_scatter<Tr, THREADS, ITEMS, true>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
+    } else {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+            if (wbase + i * 32 < tile_n) e[i] = ld_elem(src_tile + wbase + i * 32);
+        bad = rank_and_scatter<Tr, THREADS, ITEMS, false>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
+    }
+    if (Tr::NEEDS_STABLE || a.pass == 0) return;
+    if (!__syncthreads_or(bad)) return;
+    if (tid == 0) atomicAdd(a.stats, 1u);
+    rerank_tile<Tr, THREADS, ITEMS>(sh.tile, smem_raw, SM::TILE_BYTES, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
+}
+
+// ---- TMA bulk copy + mbarrier (sm_90+ PTX; SASS: UBLKCP / SYNCS) ------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "B200_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra B200_DONE_%=;\n"
+        "bra B200_WAIT_%=;\n"
+        "B200_DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src_gmem, uint32_t bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
+template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+onesweep_persistent_kernel(const __grid_constant__ PassArgs<Tr> a) {
+    using E = typename Tr::elem_t;
+    using SM = PassSmem<Tr, THREADS, ITEMS>;
+    constexpr int WARPS = THREADS / 32;
+    constexpr int TILE = THREADS * ITEMS;
+    constexpr uint32_t TILE_BYTES = (uint32_t)SM::TILE_BYTES;
+    static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit needed");
+    static_assert(TILE_BYTES % 16 == 0, "TMA bulk copies move multiples of 16 bytes");
+
+    const PassPlan pp = a.plan->pass[a.pass];
+    if (pp.skip) return;
+
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    PassShared<Tr, THREADS, ITEMS> sh(smem_raw, 2 * SM::TILE_BYTES);
+    E* const ring = reinterpret_cast<E*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
+
+    const E* __restrict__ src = (pp.src_is_tmp ? a.tmp : a.keys) + a.portion_off;
+    E* __restrict__ dst = pp.src_is_tmp ? a.keys : a.tmp;
+    const uint32_t full_tiles = a.portion_n / (uint32_t)TILE;  // tiles 0..full_tiles-1 are whole
+
+    // thread 0 is the producer: it draws tickets and starts the bulk copies.  A
+    // CTA holds at most two tickets: the tile it is ranking and the next one, drawn
+    // one tile-time later, so the tiles in flight stay a dense window of the lowest
+    // unfinished ids (a tile's look-back spins on the tile just before it).
+    auto fetch = [&](int slot, uint32_t t) {
+        sh.misc[slot] = t;
+        if (t < full_tiles) {
+            mbar_expect_tx(&sh.mbar[slot], TILE_BYTES);
+            bulk_load(ring + (size_t)slot * TILE, src + (size_t)t * TILE, TILE_BYTES, &sh.mbar[slot]);
+        }
+    };
+    if (tid == 0) {
+        mbar_init(&sh.mbar[0], 1);
+        mbar_init(&sh.mbar[1], 1);
+        fence_mbar_init();
+        fetch(0, atomicAdd(a.ticket, 1u));
+    }
+#pragma unroll
+    for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
+    __syncthreads();
+
+    for (uint32_t it = 0;; ++it) {
+        const int slot = (int)(it & 1u);
+        const uint32_t tile = sh.misc[slot];
+        if (tile >= a.num_tiles) break;
+        // ticket of the tile that goes into the other slot: asked for now, used
+        // after the count phase, when the atomic has long returned
+        uint32_t next = 0;
+        if (tid == 0) next = atomicAdd(a.ticket, 1u);
+        auto prefetch = [&]() {
+            if (tid == 0) fetch(slot ^ 1, next);
+        };
+        sh.tile = ring + (size_t)slot * TILE;
+        const E* src_tile = src + (size_t)tile * TILE;
+        E e[ITEMS];
+        bool bad;
+        uint32_t tile_n = (uint32_t)TILE;
+        if (tile < full_tiles) {
+            mbar_wait(&sh.mbar[slot], (it >> 1) & 1u);
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i) e[i] = sh.tile[wbase + i * 32];
+            bad = rank_and_scatter<Tr, THREADS, ITEMS, true>(sh, a, pp, e, dst, tile, tile_n, prefetch);
+        } else {  // the ragged last tile of the portion: plain guarded loads
+            tile_n = a.portion_n - tile * (uint32_t)TILE;
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i)
+                if (wbase + i * 32 < tile_n) e[i] = ld_elem(src_tile + wbase + i * 32);
+            bad = rank_and_scatter<Tr, THREADS, ITEMS, false>(sh, a, pp, e, dst, tile, tile_n, prefetch);
+        }
+        // counters are free once the scatter is over (barrier inside rank_and_scatter)
+#pragma unroll
+        for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
+        fence_proxy_async();  // generic-proxy accesses of this slot before the next bulk copy into it
+        if (__syncthreads_or(bad)) {
+            if (tid == 0) atomicAdd(a.stats, 1u);
+            rerank_tile<Tr, THREADS, ITEMS>(sh.tile, smem_raw, 2 * SM::TILE_BYTES, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
+            for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
+            fence_proxy_async();
+            __syncthreads();
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------

@@ -222,11 +222,11 @@ def test_demo_shapes_pairs_payload_zero(cuda):
 
 # ---- kernel variants, alignment, re-entrancy, graphs --------------------------------
 
-@pytest.mark.parametrize("kind,kb,nvar", [("u8", 1, 3), ("u16", 2, 3), ("u32", 4, 8), ("u64", 8, 8), ("u128", 16, 4)])
-def test_every_kernel_variant(kind, kb, nvar, cuda):
+@pytest.mark.parametrize("kind,kb", [("u8", 1), ("u16", 2), ("u32", 4), ("u64", 8), ("u128", 16)])
+def test_every_kernel_variant(kind, kb, cuda):
     a = _ref.random_keys(kind, 777_777, seed=3)
     try:
-        for v in range(nvar):
+        for v in range(rs.num_variants(kb)):
             rs.set_variant(kb, v)
             _check_device(a, kind, cuda)
     finally:

@@ -12,7 +12,6 @@ import torch
 import radix_sort_b200 as rs
 from radix_sort_b200 import distr, verify
 
-NVAR = {1: 3, 2: 3, 4: 8, 8: 8, 16: 4}
 
 
 def main():
@@ -26,7 +25,7 @@ def main():
     ap.add_argument("--check", action="store_true")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
-    peak = 6547.8
+    peak = 6552.0
     for kname in a.kinds.split(","):
         k = rs.Kind[kname.upper()]
         kb = rs.key_bytes(k)
@@ -36,7 +35,7 @@ def main():
             fp = verify.fingerprint(src, k) if a.check else None
             keys = torch.empty_like(src)
             ws = torch.empty(rs.temp_bytes(n, k), dtype=torch.uint8, device=dev)
-            variants = range(NVAR[kb]) if a.variants == "all" else [int(v) for v in a.variants.split(",")]
+            variants = range(rs.num_variants(kb)) if a.variants == "all" else [int(v) for v in a.variants.split(",")]
             for v in variants:
                 rs.set_variant(kb, v)
                 best = None
