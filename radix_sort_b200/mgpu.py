@@ -1,0 +1,190 @@
+"""Multi-GPU sort: one process per GPU (torch.distributed), keys sharded.
+
+The reference has no multi-device code; its only analogue is the chunk
+dimension of the scan (mod.rs:110-120).  LSD passes are global permutations, so
+the shards cannot be sorted independently: the keys are MSD-partitioned ONCE by
+G-1 splitters, buckets are exchanged all-to-all (NCCL over NVLink / NVSwitch),
+and every GPU then LSD-sorts what it received with the single-GPU kernels.
+Rank r ends up holding the r-th contiguous range of the global order, so the
+concatenation of the shards in rank order is the reference's output.
+
+    1. sample    every rank draws S keys at fixed pseudo-random positions
+    2. splitters all_gather(samples) -> every rank sorts the G*S samples (on its
+                 GPU, with the library's own sort) and picks the same G-1 quantiles
+    3. K7        b200sort_partition_device: stable partition by destination
+                 rank + per-destination counts (one onesweep pass keyed by rank)
+    4. counts    all_gather(counts) -> receive counts / offsets
+    5. exchange  all_to_all_single with split sizes (ncclSend/ncclRecv pairs)
+    6. local     b200sort_keys_device on the received keys
+
+Equal keys are bit-identical for key-only sorts, so which GPU holds which copy
+of a duplicated key is unobservable; a splitter value that is heavily
+duplicated simply lands whole on one rank (load imbalance, not an error).
+
+The device steps go through an `ops` object so that the host-side logic (sample
+positions, splitter choice, count exchange, offsets) runs under gloo on CPU in
+tests/ with a numpy test double; the default ops are the CUDA C ABI and fail
+loudly without a GPU.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+
+from . import _ffi
+from ._ffi import B200SortError, check
+from .api import Kind, NUMBER_OF_DIGITS, temp_bytes
+from .distr import mix64
+
+MAX_RANKS = 16  # K7 takes at most 15 splitters (include/b200sort.h)
+
+
+def sample_positions(n_local: int, samples: int, seed: int, rank: int) -> np.ndarray:
+    """`samples` pseudo-random positions in [0, n_local), identical on every run."""
+    if n_local == 0 or samples == 0:
+        return np.zeros(0, dtype=np.int64)
+    i = np.arange(samples, dtype=np.uint64)
+    u = mix64(np.uint64((seed ^ (0x9E37 * (rank + 1))) & (2**64 - 1)) ^ mix64(i))
+    return (u % np.uint64(n_local)).astype(np.int64)
+
+
+def choose_splitters(sorted_samples, world: int):
+    """G-1 quantiles of the globally sorted samples (any indexable sequence)."""
+    m = len(sorted_samples)
+    if m == 0:
+        return []
+    return [sorted_samples[min(m - 1, (m * (j + 1)) // world)] for j in range(world - 1)]
+
+
+def exchange_plan(count_matrix: np.ndarray, rank: int):
+    """count_matrix[s][d] = keys rank s sends to rank d.  Returns (send_counts,
+    recv_counts) of `rank` as python int lists."""
+    cm = np.asarray(count_matrix, dtype=np.int64)
+    return [int(x) for x in cm[rank, :]], [int(x) for x in cm[:, rank]]
+
+
+class CudaOps:
+    """Device steps on the current CUDA device through the C ABI."""
+
+    def __init__(self, device):
+        import torch
+        if not torch.cuda.is_available():
+            raise B200SortError(3, "multi-GPU sort needs CUDA devices (there is no CPU fallback)")
+        self.torch = torch
+        self.device = device
+        self.lib = _ffi.lib()
+
+    def _stream(self):
+        return ctypes.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+
+    def gather_samples(self, keys, positions: np.ndarray):
+        idx = self.torch.from_numpy(positions).to(self.device)
+        return keys.reshape(keys.shape[0], -1)[idx].reshape((-1,) + tuple(keys.shape[1:])).contiguous()
+
+    def empty_like_n(self, keys, n: int):
+        return self.torch.empty((n,) + tuple(keys.shape[1:]), dtype=keys.dtype, device=self.device)
+
+    def local_sort(self, keys, kind: Kind, workspace=None):
+        n = keys.shape[0]
+        if n == 0:
+            return
+        need = temp_bytes(n, kind)
+        if workspace is None or workspace.numel() < need:
+            workspace = self.torch.empty(need, dtype=self.torch.uint8, device=self.device)
+        check(self.lib.b200sort_keys_device(keys.data_ptr(), workspace.data_ptr(), workspace.numel(), n, int(kind),
+                                            self._stream()))
+        workspace.record_stream(self.torch.cuda.current_stream(self.device))
+
+    def partition(self, keys, out, kind: Kind, splitters_host: np.ndarray, workspace=None):
+        """K7.  Returns the per-destination counts as a device int64 tensor."""
+        n = keys.shape[0]
+        nsplit = len(splitters_host)
+        counts = self.torch.zeros(nsplit + 1, dtype=self.torch.int64, device=self.device)
+        need = temp_bytes(max(n, 1), kind)
+        if workspace is None or workspace.numel() < need:
+            workspace = self.torch.empty(need, dtype=self.torch.uint8, device=self.device)
+        spl = np.ascontiguousarray(splitters_host)
+        check(self.lib.b200sort_partition_device(keys.data_ptr(), out.data_ptr(), workspace.data_ptr(), workspace.numel(),
+                                                 n, int(kind), spl.ctypes.data if nsplit else None, nsplit,
+                                                 counts.data_ptr(), self._stream()))
+        workspace.record_stream(self.torch.cuda.current_stream(self.device))
+        return counts
+
+    def to_host(self, t) -> np.ndarray:
+        return t.cpu().numpy()
+
+    def from_host(self, a: np.ndarray):
+        return self.torch.from_numpy(a).to(self.device)
+
+
+@dataclass
+class ShardedResult:
+    keys: object          # this rank's range of the global order (tensor, length n_out)
+    n_out: int
+    send_counts: list
+    recv_counts: list
+    splitters: np.ndarray  # raw key bit patterns, host
+
+
+def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 << 14, seed: int = 0xB200,
+                 workspace=None, send_buffer=None) -> ShardedResult:
+    """Sort keys sharded over the ranks of `group`.  `keys`: this rank's shard
+    (CUDA tensor; (n, 2) uint64 for 128-bit kinds).  Collective: every rank of
+    the group must call it.  Returns this rank's slice of the sorted order."""
+    import torch
+    import torch.distributed as dist
+    k = Kind(kind)
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    if world > MAX_RANKS:
+        raise B200SortError(1, f"at most {MAX_RANKS} ranks (K7 takes 15 splitters)")
+    if ops is None:
+        ops = CudaOps(keys.device)
+    n_local = int(keys.shape[0])
+
+    if world == 1:
+        ops.local_sort(keys, k, workspace)
+        return ShardedResult(keys, n_local, [n_local], [n_local], np.zeros(0, dtype=ops.to_host(keys[:0]).dtype))
+
+    # 1-2. splitters from a global sample
+    pos = sample_positions(n_local, samples_per_rank, seed, rank)
+    mine = ops.gather_samples(keys, pos)
+    cnt = torch.tensor([mine.shape[0]], dtype=torch.int64, device=mine.device)
+    cnts = [torch.zeros_like(cnt) for _ in range(world)]
+    dist.all_gather(cnts, cnt, group=group)
+    sizes = [int(c.item()) for c in cnts]
+    padded = ops.empty_like_n(mine, samples_per_rank)
+    padded[: mine.shape[0]] = mine
+    gathered = [torch.empty_like(padded) for _ in range(world)]
+    dist.all_gather(gathered, padded, group=group)
+    allsamp = torch.cat([g[:s] for g, s in zip(gathered, sizes)], dim=0).contiguous()
+    ops.local_sort(allsamp, k)
+    samp_host = ops.to_host(allsamp)
+    splitters = choose_splitters(samp_host, world)
+    if len(splitters) != world - 1:  # no keys anywhere
+        return ShardedResult(keys[:0], 0, [0] * world, [0] * world, samp_host[:0])
+    splitters = np.ascontiguousarray(np.stack(splitters)) if samp_host.ndim > 1 else np.array(splitters, dtype=samp_host.dtype)
+
+    # 3. K7: partition by destination rank
+    if send_buffer is None or send_buffer.shape[0] < n_local:
+        send_buffer = ops.empty_like_n(keys, n_local)
+    send = send_buffer[:n_local]
+    counts = ops.partition(keys, send, k, splitters, workspace)
+
+    # 4. count matrix
+    rows = [torch.zeros_like(counts) for _ in range(world)]
+    dist.all_gather(rows, counts, group=group)
+    cm = np.stack([ops.to_host(r) for r in rows])
+    send_counts, recv_counts = exchange_plan(cm, rank)
+    n_out = sum(recv_counts)
+
+    # 5. all-to-all (rows of 128-bit keys are 2 x uint64: split sizes count rows)
+    recv = ops.empty_like_n(keys, n_out)
+    dist.all_to_all_single(recv, send, output_split_sizes=recv_counts, input_split_sizes=send_counts, group=group)
+
+    # 6. local LSD sort of the received range
+    ops.local_sort(recv, k, workspace)
+    return ShardedResult(recv, n_out, send_counts, recv_counts, splitters)
