@@ -46,37 +46,37 @@ template <> struct FamilyTraits<FAM_RECORDS, 16> { using type = RecordTraits<u12
 // ---- K3 variants ------------------------------------------------------------------
 // kernel: 0 = onesweep_pass_kernel (one tile per CTA, any alignment)
 //         1 = onesweep_persistent_kernel (TMA ring; 16-byte aligned buffers)
-// Index 0 of a table is the default; B200_FALLBACK_VARIANT names the one-tile
-// variant used when a buffer is not 16-byte aligned.  The other entries exist
+// Index 0 of a table is the default (the fastest measured on B200, profiles/);
+// FALLBACK names the one-tile variant used when a buffer is not 16-byte aligned.  The other entries exist
 // for on-GPU sweeps (b200sort_set_variant).  The counts are repeated as macros
 // because the dispatcher and the build script need them in the preprocessor.
-struct VariantDesc { int kernel, threads, items, min_blocks; };
+struct VariantDesc { int kernel, threads, items, min_blocks, lbt; };  // threads = worker threads; lbt = look-back threads
 
 template <int FAM, int W> struct Variants;
 #define B200_NV_KEYS_1 2
-template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{1, 512, 32, 2}, {0, 512, 32, 2}}; static constexpr int FALLBACK = 1; };
+template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}, {1, 448, 32, 2, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_2 2
-template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{1, 512, 24, 2}, {0, 512, 24, 2}}; static constexpr int FALLBACK = 1; };
+template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}, {1, 448, 24, 2, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_4 8
-template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{1, 512, 16, 2}, {0, 512, 22, 2}, {1, 512, 20, 2}, {1, 512, 22, 2}, {1, 384, 16, 3}, {1, 256, 16, 4}, {1, 256, 24, 3}, {0, 512, 16, 2}}; static constexpr int FALLBACK = 1; };
+template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 22, 2, 0}, {1, 448, 16, 2, 64}, {1, 512, 16, 2, 64}, {1, 384, 20, 2, 128}, {1, 448, 20, 2, 64}, {1, 384, 22, 2, 64}, {1, 384, 16, 3, 64}, {1, 384, 16, 2, 128}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_8 8
-template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{1, 512, 8, 2}, {0, 512, 16, 2}, {1, 512, 10, 2}, {1, 512, 11, 2}, {1, 384, 8, 3}, {1, 256, 8, 4}, {1, 256, 12, 3}, {0, 512, 12, 2}}; static constexpr int FALLBACK = 1; };
+template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {1, 448, 8, 2, 64}, {1, 384, 12, 2, 128}, {1, 448, 10, 2, 64}, {1, 448, 12, 2, 64}, {1, 384, 12, 2, 64}, {1, 384, 8, 3, 64}, {1, 384, 10, 2, 128}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_16 3
-template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{1, 256, 8, 3}, {0, 256, 12, 2}, {1, 512, 5, 2}}; static constexpr int FALLBACK = 1; };
+template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {1, 256, 8, 3, 64}, {1, 448, 5, 2, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_RECORDS_8 3
-template <> struct Variants<FAM_RECORDS, 8> { static constexpr VariantDesc v[] = {{1, 512, 8, 2}, {0, 512, 12, 2}, {1, 512, 10, 2}}; static constexpr int FALLBACK = 1; };
+template <> struct Variants<FAM_RECORDS, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0}, {1, 448, 8, 2, 64}, {1, 448, 10, 2, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_RECORDS_16 3
-template <> struct Variants<FAM_RECORDS, 16> { static constexpr VariantDesc v[] = {{1, 256, 8, 3}, {0, 256, 12, 2}, {1, 512, 5, 2}}; static constexpr int FALLBACK = 1; };
+template <> struct Variants<FAM_RECORDS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {1, 256, 8, 3, 64}, {1, 448, 5, 2, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_PARTITION_1 1
-template <> struct Variants<FAM_PARTITION, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_PARTITION, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_PARTITION_2 1
-template <> struct Variants<FAM_PARTITION, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_PARTITION, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_PARTITION_4 1
-template <> struct Variants<FAM_PARTITION, 4> { static constexpr VariantDesc v[] = {{0, 512, 16, 2}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_PARTITION, 4> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_PARTITION_8 1
-template <> struct Variants<FAM_PARTITION, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_PARTITION, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_PARTITION_16 1
-template <> struct Variants<FAM_PARTITION, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_PARTITION, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}}; static constexpr int FALLBACK = 0; };
 
 template <int FAM, int W> constexpr int num_variants() { return (int)(sizeof(Variants<FAM, W>::v) / sizeof(VariantDesc)); }
 
@@ -87,12 +87,12 @@ struct VariantEntry {
     static cudaError_t launch(const PassArgs<typename FamilyTraits<FAM, W>::type>& a, cudaStream_t st);
 };
 
-template <typename Tr, int KERNEL, int THREADS, int ITEMS, int MINB>
+template <typename Tr, int KERNEL, int THREADS, int ITEMS, int MINB, int LBT>
 struct PassLauncher {
     using SM = PassSmem<Tr, THREADS, ITEMS>;
     static constexpr size_t SMEM = KERNEL == 1 ? SM::TOTAL_PERSISTENT : SM::TOTAL;
     static auto kernel() {
-        if constexpr (KERNEL == 1) return onesweep_persistent_kernel<Tr, THREADS, ITEMS, MINB>;
+        if constexpr (KERNEL == 1) return onesweep_persistent_kernel<Tr, THREADS, ITEMS, LBT, MINB>;
         else return onesweep_pass_kernel<Tr, THREADS, ITEMS, MINB>;
     }
     // per-device one-time setup: opt in to the dynamic shared memory, read the occupancy
@@ -107,7 +107,7 @@ struct PassLauncher {
             e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
             if (e != cudaSuccess) return e;
             int per_sm = 0, sms = 0;
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, THREADS, SMEM);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, THREADS + LBT, SMEM);
             if (e != cudaSuccess) return e;
             e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
             if (e != cudaSuccess) return e;
@@ -124,7 +124,7 @@ struct PassLauncher {
         if (e != cudaSuccess) return e;
         unsigned grid = a.num_tiles;
         if (KERNEL == 1 && grid > (unsigned)resident) grid = (unsigned)resident;
-        kernel()<<<grid, THREADS, SMEM, st>>>(a);
+        kernel()<<<grid, THREADS + LBT, SMEM, st>>>(a);
         count_launch();
         return cudaGetLastError();
     }

@@ -320,6 +320,47 @@ __device__ __forceinline__ void column_bases(uint32_t* warp_hist, int d, uint32_
     }
 }
 
+// ---- named barriers (bar.sync / bar.arrive id, count): the persistent kernel
+// splits its CTA into worker warps and look-back warps that meet only at the
+// hand-over points, so the CTA-wide barrier 0 cannot be used inside the tile loop
+template <int ID, int COUNT>
+__device__ __forceinline__ void bar_sync() {
+    asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(COUNT) : "memory");
+}
+template <int ID, int COUNT>
+__device__ __forceinline__ void bar_arrive() {
+    asm volatile("bar.arrive %0, %1;" ::"n"(ID), "n"(COUNT) : "memory");
+}
+template <int ID, int COUNT>
+__device__ __forceinline__ bool bar_red_or(bool p) {
+    int r;
+    asm volatile(
+        "{\n"
+        ".reg .pred p, q;\n"
+        "setp.ne.s32 p, %1, 0;\n"
+        "bar.red.or.pred q, %2, %3, p;\n"
+        "selp.s32 %0, 1, 0, q;\n"
+        "}\n" : "=r"(r) : "r"((int)p), "n"(ID), "n"(COUNT) : "memory");
+    return r != 0;
+}
+constexpr int BAR_WORKERS = 1;   // worker warps only
+constexpr int BAR_CNT = 2;       // workers arrive: sh.cnt + the published partial are ready; look-back warps wait
+constexpr int BAR_EXCL = 3;      // workers arrive: sh.excl is ready; look-back warps wait
+constexpr int BAR_GPTR = 4;      // look-back warps arrive: sh.gptr is ready; workers wait
+
+// barrier among the threads that rank keys: the whole CTA when the look-back is
+// done in line (LBT == 0), the worker warps otherwise
+template <int WORKERS, int LBT>
+__device__ __forceinline__ void workers_sync() {
+    if constexpr (LBT == 0) __syncthreads();
+    else bar_sync<BAR_WORKERS, WORKERS>();
+}
+template <int WORKERS, int LBT>
+__device__ __forceinline__ bool workers_sync_or(bool p) {
+    if constexpr (LBT == 0) return __syncthreads_or(p) != 0;
+    else return bar_red_or<BAR_WORKERS, WORKERS>(p);
+}
+
 // Decoupled look-back for one digit, LB_BATCH predecessors per round trip.
 // p points at the status word of tile `pos` (the nearest predecessor) for this
 // digit; tiles below 0 read as {INCLUSIVE, 0}.
@@ -376,7 +417,7 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
 // Slow path, out of line: rebuild the tile with ballot ranks (lane-ordered by
 // construction) from the keys still in global memory, and rewrite its slots.
 // Entered by a whole CTA; warp_hist may hold anything; excl/gptr are valid.
-template <typename Tr, int THREADS, int ITEMS>
+template <typename Tr, int THREADS, int ITEMS, int LBT>
 __device__ __noinline__ void rerank_tile(typename Tr::elem_t* tile_buf, unsigned char* aux_minus_tiles, size_t tile_bytes_total,
                                          const PassArgs<Tr>* ap, const typename Tr::elem_t* src_tile,
                                          uint32_t tile_n, uint32_t xf_in, uint32_t xf_out) {
@@ -389,9 +430,9 @@ __device__ __noinline__ void rerank_tile(typename Tr::elem_t* tile_buf, unsigned
     const unsigned lane_lt = (1u << lane) - 1u;
     const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
     uint32_t* my_hist = sh.warp_hist + warp * RADIX;
-    __syncthreads();
+    workers_sync<THREADS, LBT>();
     for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
-    __syncthreads();
+    workers_sync<THREADS, LBT>();
     E e[ITEMS];
     uint32_t rank[ITEMS];
 #pragma unroll
@@ -403,15 +444,15 @@ __device__ __noinline__ void rerank_tile(typename Tr::elem_t* tile_buf, unsigned
         }
         rank[i] = ballot_rank<false>(Tr::digit(e[i], a.pass, a.prm), valid, my_hist, lane, lane_lt);
     }
-    __syncthreads();
+    workers_sync<THREADS, LBT>();
     if (tid < RADIX) column_bases<WARPS>(sh.warp_hist, tid, sh.excl[tid]);
-    __syncthreads();
+    workers_sync<THREADS, LBT>();
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i)
         if (wbase + i * 32 < tile_n) sh.tile[rank[i] + my_hist[Tr::digit(e[i], a.pass, a.prm)]] = e[i];
-    __syncthreads();
+    workers_sync<THREADS, LBT>();
     write_out<Tr, THREADS, ITEMS, false, false>(sh, a, xf_out, tile_n, tid);
-    __syncthreads();
+    workers_sync<THREADS, LBT>();
 }
 
 // One tile whose keys are already in registers (warp-striped: item i of lane l =
@@ -422,14 +463,17 @@ __device__ __noinline__ void rerank_tile(typename Tr::elem_t* tile_buf, unsigned
 // Returns true when the order check of the write-out failed (caller re-ranks).
 struct NoHook { __device__ __forceinline__ void operator()() const {} };
 
-template <typename Tr, int THREADS, int ITEMS, bool FULL, typename Hook>
-__device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, THREADS, ITEMS>& sh, const PassArgs<Tr>& a,
+// WORKERS threads rank the tile.  LBT == 0: the last 256 of them also run the
+// look-back, in line.  LBT > 0: LBT extra threads (the look-back warps of the
+// persistent kernel) run it concurrently and hand sh.gptr over at BAR_GPTR.
+template <typename Tr, int WORKERS, int ITEMS, bool FULL, int LBT, typename Hook>
+__device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, ITEMS>& sh, const PassArgs<Tr>& a,
                                                  const PassPlan& pp, typename Tr::elem_t (&e)[ITEMS],
                                                  typename Tr::elem_t* __restrict__ dst, uint32_t tile, uint32_t tile_n,
                                                  Hook after_count) {
     using E = typename Tr::elem_t;
-    constexpr int WARPS = THREADS / 32;
-    constexpr int LB0 = THREADS - RADIX;  // the last 256 threads run the look-back
+    constexpr int WARPS = WORKERS / 32;
+    constexpr int LB0 = WORKERS - RADIX;  // in-line look-back: the last 256 threads
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int pass = a.pass;
     const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
@@ -453,7 +497,7 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, THREADS, I
         for (int i = 0; i < ITEMS; ++i)
             if (FULL || wbase + i * 32 < tile_n) atomicAdd(&my_hist[Tr::digit(e[i], pass, a.prm)], 1u);
     }
-    __syncthreads();
+    workers_sync<WORKERS, LBT>();
     after_count();  // persistent kernel: thread 0 starts the bulk copy of the next tile
 
     // ---- 2. thread d owns digit d: tile count -> publish -> scan over digits ->
@@ -463,11 +507,9 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, THREADS, I
     if (tid < RADIX) {
         count = column_total<WARPS>(sh.warp_hist, tid);
         st_relaxed_u32(lb + tid, (tile == 0 ? LB_FLAG_INCLUSIVE : LB_FLAG_PARTIAL) | count);
+        sh.cnt[tid] = count;
     }
-    // the look-back threads ask for the first batch of predecessors now; the
-    // answers arrive while the scan and the scatter run
-    LookBack look;
-    if (tid >= LB0) look.request(lb - RADIX + (tid - LB0), (int)tile - 1);
+    if constexpr (LBT > 0) bar_arrive<BAR_CNT, WORKERS + LBT>();  // the look-back warps start now
     uint32_t incl = count;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -475,17 +517,17 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, THREADS, I
         if (lane >= o) incl += y;
     }
     if (lane == 31 && warp < RADIX / 32) sh.misc[2 + warp] = incl;
-    __syncthreads();
+    workers_sync<WORKERS, LBT>();
     if (tid < RADIX) {
         uint32_t base = 0;
 #pragma unroll
         for (int w = 0; w < RADIX / 32; ++w) base += (w < warp) ? sh.misc[2 + w] : 0u;
         const uint32_t excl = base + incl - count;  // keys of the tile with a smaller digit
         sh.excl[tid] = excl;
-        sh.cnt[tid] = count;
         column_bases<WARPS>(sh.warp_hist, tid, excl);
     }
-    __syncthreads();
+    if constexpr (LBT > 0) bar_arrive<BAR_EXCL, WORKERS + LBT>();
+    workers_sync<WORKERS, LBT>();
 
     // ---- 3. scatter: the returned counter value IS the key's slot in the tile
 #pragma unroll
@@ -496,28 +538,106 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, THREADS, I
             sh.tile[slot] = e[i];
         }
 
-    // ---- decoupled look-back, one digit per thread of the last 256 threads
-    if (tid >= LB0) {
-        const int d = tid - LB0;
-        const uint32_t cnt_d = sh.cnt[d];
-        unsigned long long excl_tiles = 0;
-        if (tile > 0) {
-            const uint32_t sum = look.resolve(lb - RADIX + d, (int)tile - 1);
-            st_relaxed_u32(lb + d, LB_FLAG_INCLUSIVE | (sum + cnt_d));
-            excl_tiles = sum;
+    if constexpr (LBT == 0) {
+        // ---- decoupled look-back in line, one digit per thread of the last 256 threads
+        if (tid >= LB0) {
+            const int d = tid - LB0;
+            const uint32_t cnt_d = sh.cnt[d];
+            unsigned long long excl_tiles = 0;
+            if (tile > 0) {
+                LookBack look;
+                look.request(lb - RADIX + d, (int)tile - 1);
+                const uint32_t sum = look.resolve(lb - RADIX + d, (int)tile - 1);
+                st_relaxed_u32(lb + d, LB_FLAG_INCLUSIVE | (sum + cnt_d));
+                excl_tiles = sum;
+            }
+            const unsigned long long gbase = a.bins_in[d] + excl_tiles;
+            sh.gptr[d] = (unsigned long long)dst + (gbase - sh.excl[d]) * sizeof(E);
+            if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[d] = gbase + cnt_d;
         }
-        const unsigned long long gbase = a.bins_in[d] + excl_tiles;
-        sh.gptr[d] = (unsigned long long)dst + (gbase - sh.excl[d]) * sizeof(E);
-        if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[d] = gbase + cnt_d;
+        __syncthreads();
+    } else {
+        bar_sync<BAR_GPTR, WORKERS + LBT>();  // scatter done by all workers + sh.gptr published
     }
-    __syncthreads();
 
     // ---- coalesced run write-out; key-only passes check the order of the tile
     if (Tr::NEEDS_STABLE || pass == 0) {
-        write_out<Tr, THREADS, ITEMS, FULL, false>(sh, a, pp.xf_out, tile_n, tid);
+        write_out<Tr, WORKERS, ITEMS, FULL, false>(sh, a, pp.xf_out, tile_n, tid);
         return false;
     }
-    return write_out<Tr, THREADS, ITEMS, FULL, true>(sh, a, pp.xf_out, tile_n, tid);
+    return write_out<Tr, WORKERS, ITEMS, FULL, true>(sh, a, pp.xf_out, tile_n, tid);
+}
+
+// The look-back warps of the persistent kernel: LBT threads, 256 / LBT digits
+// each, for one tile.  They start as soon as the tile's counts are published --
+// long before the workers need the result -- so the round trips to L2 overlap
+// the scan and the scatter, and the tile's INCLUSIVE words appear early, which
+// keeps every later tile's walk short.
+template <typename Tr, int WORKERS, int ITEMS, int LBT>
+__device__ __forceinline__ void lookback_role(const PassShared<Tr, WORKERS, ITEMS>& sh, const PassArgs<Tr>& a,
+                                              typename Tr::elem_t* dst, uint32_t tile,
+                                              const unsigned long long (&bin)[RADIX / LBT]) {
+    using E = typename Tr::elem_t;
+    constexpr int NDL = RADIX / LBT;
+    const int ltid = (int)threadIdx.x - WORKERS;
+    uint32_t* lb = a.lookback + (size_t)tile * RADIX;
+    bar_sync<BAR_CNT, WORKERS + LBT>();
+    // All NDL digits of a thread walk back together: every round trip to L2 asks
+    // for the next LB_BATCH predecessors of every digit that is still open.  A
+    // batch that contains a word not yet published is asked for again as a whole
+    // (never word by word: serial re-polls multiply the latency, and the depth of
+    // everybody's walk grows with that latency).
+    uint32_t sum[NDL];
+    int pos[NDL];  // nearest predecessor not yet summed; < 0: closed
+#pragma unroll
+    for (int q = 0; q < NDL; ++q) { sum[q] = 0; pos[q] = (int)tile - 1; }
+    const uint32_t* col = a.lookback + ltid;  // status word of tile 0, digit ltid
+    for (;;) {
+        bool any = false;
+#pragma unroll
+        for (int q = 0; q < NDL; ++q) any |= pos[q] >= 0;
+        if (!any) break;
+        uint32_t v[NDL][LB_BATCH];
+#pragma unroll
+        for (int q = 0; q < NDL; ++q)
+#pragma unroll
+            for (int j = 0; j < LB_BATCH; ++j)
+                v[q][j] = (pos[q] - j >= 0) ? ld_relaxed_u32(col + q * LBT + (size_t)(pos[q] - j) * RADIX) : LB_FLAG_INCLUSIVE;
+#pragma unroll
+        for (int q = 0; q < NDL; ++q) {
+            if (pos[q] < 0) continue;
+            uint32_t part = 0;
+            int state = 0;  // 0 walking, 1 reached an inclusive prefix, 2 met an unpublished word
+#pragma unroll
+            for (int j = 0; j < LB_BATCH; ++j) {
+                const uint32_t x = v[q][j];
+                if (state == 0) {
+                    if ((x & (LB_FLAG_PARTIAL | LB_FLAG_INCLUSIVE)) == 0) state = 2;
+                    else {
+                        part += x & LB_VALUE_MASK;
+                        if (x & LB_FLAG_INCLUSIVE) state = 1;
+                    }
+                }
+            }
+            if (state == 2) continue;  // ask for the same batch again
+            sum[q] += part;
+            if (state == 1) {
+                pos[q] = -1;
+                st_relaxed_u32(lb + q * LBT + ltid, LB_FLAG_INCLUSIVE | (sum[q] + sh.cnt[q * LBT + ltid]));
+            } else {
+                pos[q] -= LB_BATCH;
+            }
+        }
+    }
+    bar_sync<BAR_EXCL, WORKERS + LBT>();
+#pragma unroll
+    for (int q = 0; q < NDL; ++q) {
+        const int d = q * LBT + ltid;
+        const unsigned long long gbase = bin[q] + sum[q];
+        sh.gptr[d] = (unsigned long long)dst + (gbase - sh.excl[d]) * sizeof(E);
+        if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[d] = gbase + sh.cnt[d];
+    }
+    bar_arrive<BAR_GPTR, WORKERS + LBT>();
 }
 
 template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS>
@@ -554,17 +674,17 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     if (tile_n == (uint32_t)TILE) {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) e[i] = ld_elem(src_tile + wbase + i * 32);
-        bad = rank_and_scatter<Tr, THREADS, ITEMS, true>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
+        bad = rank_and_scatter<Tr, THREADS, ITEMS, true, 0>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
     } else {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
             if (wbase + i * 32 < tile_n) e[i] = ld_elem(src_tile + wbase + i * 32);
-        bad = rank_and_scatter<Tr, THREADS, ITEMS, false>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
+        bad = rank_and_scatter<Tr, THREADS, ITEMS, false, 0>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
     }
     if (Tr::NEEDS_STABLE || a.pass == 0) return;
     if (!__syncthreads_or(bad)) return;
     if (tid == 0) atomicAdd(a.stats, 1u);
-    rerank_tile<Tr, THREADS, ITEMS>(sh.tile, smem_raw, SM::TILE_BYTES, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
+    rerank_tile<Tr, THREADS, ITEMS, 0>(sh.tile, smem_raw, SM::TILE_BYTES, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
 }
 
 // ---- TMA bulk copy + mbarrier (sm_90+ PTX; SASS: UBLKCP / SYNCS) ------------------
@@ -593,22 +713,23 @@ __device__ __forceinline__ void bulk_load(void* dst_smem, const void* src_gmem, 
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
-template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS>
-__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+template <typename Tr, int WORKERS, int ITEMS, int LBT, int MIN_BLOCKS>
+__global__ void __launch_bounds__(WORKERS + LBT, MIN_BLOCKS)
 onesweep_persistent_kernel(const __grid_constant__ PassArgs<Tr> a) {
     using E = typename Tr::elem_t;
-    using SM = PassSmem<Tr, THREADS, ITEMS>;
-    constexpr int WARPS = THREADS / 32;
-    constexpr int TILE = THREADS * ITEMS;
+    using SM = PassSmem<Tr, WORKERS, ITEMS>;
+    constexpr int WARPS = WORKERS / 32;
+    constexpr int TILE = WORKERS * ITEMS;
     constexpr uint32_t TILE_BYTES = (uint32_t)SM::TILE_BYTES;
-    static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit needed");
+    static_assert(WORKERS >= RADIX && WORKERS % 32 == 0, "one worker thread per digit needed");
+    static_assert(LBT >= 32 && LBT % 32 == 0 && RADIX % LBT == 0, "look-back warps own 256 / LBT digits per thread");
     static_assert(TILE_BYTES % 16 == 0, "TMA bulk copies move multiples of 16 bytes");
 
     const PassPlan pp = a.plan->pass[a.pass];
     if (pp.skip) return;
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    PassShared<Tr, THREADS, ITEMS> sh(smem_raw, 2 * SM::TILE_BYTES);
+    PassShared<Tr, WORKERS, ITEMS> sh(smem_raw, 2 * SM::TILE_BYTES);
     E* const ring = reinterpret_cast<E*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
@@ -634,9 +755,22 @@ onesweep_persistent_kernel(const __grid_constant__ PassArgs<Tr> a) {
         fence_mbar_init();
         fetch(0, atomicAdd(a.ticket, 1u));
     }
-#pragma unroll
-    for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
+    for (int i = tid; i < WARPS * RADIX; i += WORKERS + LBT) sh.warp_hist[i] = 0;
     __syncthreads();
+
+    if (tid >= WORKERS) {
+        // ---- look-back warps: one look-back per tile, concurrent with the workers
+        constexpr int NDL = RADIX / LBT;
+        unsigned long long bin[NDL];
+#pragma unroll
+        for (int q = 0; q < NDL; ++q) bin[q] = a.bins_in[q * LBT + (tid - WORKERS)];
+        for (uint32_t it = 0;; ++it) {
+            const uint32_t tile = sh.misc[it & 1u];
+            if (tile >= a.num_tiles) break;
+            lookback_role<Tr, WORKERS, ITEMS, LBT>(sh, a, dst, tile, bin);
+        }
+        return;
+    }
 
     for (uint32_t it = 0;; ++it) {
         const int slot = (int)(it & 1u);
@@ -658,24 +792,24 @@ onesweep_persistent_kernel(const __grid_constant__ PassArgs<Tr> a) {
             mbar_wait(&sh.mbar[slot], (it >> 1) & 1u);
 #pragma unroll
             for (int i = 0; i < ITEMS; ++i) e[i] = sh.tile[wbase + i * 32];
-            bad = rank_and_scatter<Tr, THREADS, ITEMS, true>(sh, a, pp, e, dst, tile, tile_n, prefetch);
+            bad = rank_and_scatter<Tr, WORKERS, ITEMS, true, LBT>(sh, a, pp, e, dst, tile, tile_n, prefetch);
         } else {  // the ragged last tile of the portion: plain guarded loads
             tile_n = a.portion_n - tile * (uint32_t)TILE;
 #pragma unroll
             for (int i = 0; i < ITEMS; ++i)
                 if (wbase + i * 32 < tile_n) e[i] = ld_elem(src_tile + wbase + i * 32);
-            bad = rank_and_scatter<Tr, THREADS, ITEMS, false>(sh, a, pp, e, dst, tile, tile_n, prefetch);
+            bad = rank_and_scatter<Tr, WORKERS, ITEMS, false, LBT>(sh, a, pp, e, dst, tile, tile_n, prefetch);
         }
-        // counters are free once the scatter is over (barrier inside rank_and_scatter)
+        // counters are free once the scatter is over (BAR_GPTR inside rank_and_scatter)
 #pragma unroll
-        for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
+        for (int i = tid; i < WARPS * RADIX; i += WORKERS) sh.warp_hist[i] = 0;
         fence_proxy_async();  // generic-proxy accesses of this slot before the next bulk copy into it
-        if (__syncthreads_or(bad)) {
+        if (workers_sync_or<WORKERS, LBT>(bad)) {
             if (tid == 0) atomicAdd(a.stats, 1u);
-            rerank_tile<Tr, THREADS, ITEMS>(sh.tile, smem_raw, 2 * SM::TILE_BYTES, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
-            for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
+            rerank_tile<Tr, WORKERS, ITEMS, LBT>(sh.tile, smem_raw, 2 * SM::TILE_BYTES, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
+            for (int i = tid; i < WARPS * RADIX; i += WORKERS) sh.warp_hist[i] = 0;
             fence_proxy_async();
-            __syncthreads();
+            workers_sync<WORKERS, LBT>();
         }
     }
 }

@@ -1,0 +1,123 @@
+"""CPU, world_size 2 over gloo: the host-side logic of the multi-GPU sort
+(radix_sort_b200/mgpu.py) -- sample positions, splitter choice, count exchange,
+all-to-all plan -- with a numpy test double standing in for the device steps
+(K7 partition and the local sort).  The double lives here, in tests/: the
+product's default ops are the CUDA C ABI and refuse to run without a GPU."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from radix_sort_b200 import mgpu  # noqa: E402
+from radix_sort_b200.api import Kind  # noqa: E402
+
+
+class NumpyOps:
+    """Test double for mgpu.CudaOps on CPU tensors (u64 keys only)."""
+
+    def gather_samples(self, keys, positions):
+        return keys[torch.from_numpy(positions)].contiguous()
+
+    def empty_like_n(self, keys, n):
+        return torch.empty((n,) + tuple(keys.shape[1:]), dtype=keys.dtype)
+
+    def local_sort(self, keys, kind, workspace=None):
+        a = keys.numpy().view(np.uint64)
+        a[...] = np.sort(a, kind="stable")
+
+    def partition(self, keys, out, kind, splitters_host, workspace=None):
+        a = keys.numpy().view(np.uint64)
+        dest = np.searchsorted(splitters_host.view(np.uint64), a, side="right")  # #{j : spl[j] <= key}
+        order = np.argsort(dest, kind="stable")
+        out.numpy().view(np.uint64)[...] = a[order]
+        return torch.from_numpy(np.bincount(dest, minlength=len(splitters_host) + 1).astype(np.int64))
+
+    def to_host(self, t):
+        return t.numpy()
+
+    def from_host(self, a):
+        return torch.from_numpy(a)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, n_per_rank, mode, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(1000 + rank)
+        if mode == "uniform":
+            a = rng.integers(0, 2**63, size=n_per_rank, dtype=np.int64)
+        elif mode == "few_unique":
+            a = rng.integers(0, 5, size=n_per_rank, dtype=np.int64) * 1000
+        else:  # ragged: rank 1 holds nothing
+            a = rng.integers(0, 2**63, size=n_per_rank if rank == 0 else 0, dtype=np.int64)
+        keys = torch.from_numpy(a.copy())
+        # uint64 keys travel as int64 tensors (gloo has no uint64); values < 2^63 keep the order
+        res = mgpu.sort_sharded(keys, Kind.U64, ops=NumpyOps(), samples_per_rank=512)
+        out = res.keys.numpy().copy()
+        q.put((rank, a, out, res.send_counts, res.recv_counts))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("mode", ["uniform", "few_unique", "ragged"])
+def test_sort_sharded_world2_gloo(mode):
+    world, n = 2, 20_000
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, mode, q)) for r in range(world)]
+    [p.start() for p in procs]
+    got = {}
+    for _ in range(world):
+        r, a, out, sc, rc = q.get(timeout=120)
+        got[r] = (a, out, sc, rc)
+    [p.join(timeout=60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    whole_in = np.concatenate([got[r][0] for r in range(world)])
+    whole_out = np.concatenate([got[r][1] for r in range(world)])  # shards in rank order
+    assert np.array_equal(whole_out, np.sort(whole_in)), "concatenated shards are not the sorted input"
+    # the exchange plan is consistent: what r sends to d is what d receives from r
+    for r in range(world):
+        for d in range(world):
+            assert got[r][2][d] == got[d][3][r]
+    if mode == "uniform":  # splitters from samples balance the shards
+        sizes = [len(got[r][1]) for r in range(world)]
+        assert max(sizes) < 1.2 * sum(sizes) / world
+
+
+def test_sample_positions_and_splitters_are_deterministic():
+    p1 = mgpu.sample_positions(1000, 64, seed=7, rank=1)
+    p2 = mgpu.sample_positions(1000, 64, seed=7, rank=1)
+    assert np.array_equal(p1, p2) and p1.min() >= 0 and p1.max() < 1000
+    assert len(mgpu.sample_positions(0, 64, 7, 0)) == 0
+    s = np.arange(100)
+    assert mgpu.choose_splitters(s, 4) == [25, 50, 75]
+    assert mgpu.choose_splitters(s[:0], 4) == []
+    send, recv = mgpu.exchange_plan(np.array([[1, 2], [3, 4]]), rank=0)
+    assert send == [1, 2] and recv == [1, 3]
+
+
+def test_cuda_ops_refuse_to_run_without_a_gpu():
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(Exception) as e:
+        mgpu.CudaOps(torch.device("cpu"))
+    assert "no CPU fallback" in str(e.value) or "CUDA" in str(e.value)
