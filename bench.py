@@ -248,8 +248,9 @@ def run_gpu(args):
         # shard boundaries: my first key >= previous rank's last key
         edge = torch.zeros(2, dtype=torch.int64, device=dev)
         if out.shape[0]:
-            edge[0] = out[0].view(torch.int64) ^ (-2**63)
-            edge[1] = out[-1].view(torch.int64) ^ (-2**63)
+            o64 = out.view(torch.int64)
+            edge[0] = o64[0] ^ (-2**63)
+            edge[1] = o64[-1] ^ (-2**63)
         edges = [torch.zeros_like(edge) for _ in range(world)]
         dist.all_gather(edges, edge)
         last = None
@@ -369,7 +370,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=N_KEYS, help="keys per GPU (default: the BASELINE.json workload)")
+    ap.add_argument("--keys", dest="n", type=int, default=N_KEYS, help="keys per GPU (default: the BASELINE.json workload)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":

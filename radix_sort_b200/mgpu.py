@@ -67,7 +67,9 @@ def exchange_plan(count_matrix: np.ndarray, rank: int):
 
 
 class CudaOps:
-    """Device steps on the current CUDA device through the C ABI."""
+    """Device steps on the current CUDA device through the C ABI.  Keys travel as
+    (n, key_bytes) uint8 rows: byte tensors index, concatenate and go through
+    NCCL whatever the key type (torch has no CUDA indexing for uint64)."""
 
     def __init__(self, device):
         import torch
@@ -80,34 +82,35 @@ class CudaOps:
     def _stream(self):
         return ctypes.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
 
-    def gather_samples(self, keys, positions: np.ndarray):
+    def gather_samples(self, rows, positions: np.ndarray):
         idx = self.torch.from_numpy(positions).to(self.device)
-        return keys.reshape(keys.shape[0], -1)[idx].reshape((-1,) + tuple(keys.shape[1:])).contiguous()
+        return rows[idx].contiguous()
 
-    def empty_like_n(self, keys, n: int):
-        return self.torch.empty((n,) + tuple(keys.shape[1:]), dtype=keys.dtype, device=self.device)
+    def empty_rows(self, n: int, key_bytes: int):
+        return self.torch.empty((n, key_bytes), dtype=self.torch.uint8, device=self.device)
 
-    def local_sort(self, keys, kind: Kind, workspace=None):
-        n = keys.shape[0]
+    def local_sort(self, rows, kind: Kind, workspace=None):
+        n = rows.shape[0]
         if n == 0:
             return
         need = temp_bytes(n, kind)
         if workspace is None or workspace.numel() < need:
             workspace = self.torch.empty(need, dtype=self.torch.uint8, device=self.device)
-        check(self.lib.b200sort_keys_device(keys.data_ptr(), workspace.data_ptr(), workspace.numel(), n, int(kind),
+        check(self.lib.b200sort_keys_device(rows.data_ptr(), workspace.data_ptr(), workspace.numel(), n, int(kind),
                                             self._stream()))
         workspace.record_stream(self.torch.cuda.current_stream(self.device))
 
-    def partition(self, keys, out, kind: Kind, splitters_host: np.ndarray, workspace=None):
-        """K7.  Returns the per-destination counts as a device int64 tensor."""
-        n = keys.shape[0]
-        nsplit = len(splitters_host)
+    def partition(self, rows, out, kind: Kind, splitters_host: np.ndarray, workspace=None):
+        """K7.  splitters_host: (nsplit, key_bytes) uint8.  Returns the per-destination
+        counts as a device int64 tensor."""
+        n = rows.shape[0]
+        nsplit = int(splitters_host.shape[0])
         counts = self.torch.zeros(nsplit + 1, dtype=self.torch.int64, device=self.device)
         need = temp_bytes(max(n, 1), kind)
         if workspace is None or workspace.numel() < need:
             workspace = self.torch.empty(need, dtype=self.torch.uint8, device=self.device)
         spl = np.ascontiguousarray(splitters_host)
-        check(self.lib.b200sort_partition_device(keys.data_ptr(), out.data_ptr(), workspace.data_ptr(), workspace.numel(),
+        check(self.lib.b200sort_partition_device(rows.data_ptr(), out.data_ptr(), workspace.data_ptr(), workspace.numel(),
                                                  n, int(kind), spl.ctypes.data if nsplit else None, nsplit,
                                                  counts.data_ptr(), self._stream()))
         workspace.record_stream(self.torch.cuda.current_stream(self.device))
@@ -115,9 +118,6 @@ class CudaOps:
 
     def to_host(self, t) -> np.ndarray:
         return t.cpu().numpy()
-
-    def from_host(self, a: np.ndarray):
-        return self.torch.from_numpy(a).to(self.device)
 
 
 @dataclass
@@ -132,59 +132,68 @@ class ShardedResult:
 def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 << 14, seed: int = 0xB200,
                  workspace=None, send_buffer=None) -> ShardedResult:
     """Sort keys sharded over the ranks of `group`.  `keys`: this rank's shard
-    (CUDA tensor; (n, 2) uint64 for 128-bit kinds).  Collective: every rank of
-    the group must call it.  Returns this rank's slice of the sorted order."""
+    (contiguous CUDA tensor; (n, 2) uint64 for 128-bit kinds).  Collective: every
+    rank of the group must call it.  Returns this rank's slice of the sorted order
+    (same dtype as `keys`)."""
     import torch
     import torch.distributed as dist
     k = Kind(kind)
+    kb = NUMBER_OF_DIGITS[k]
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     if world > MAX_RANKS:
         raise B200SortError(1, f"at most {MAX_RANKS} ranks (K7 takes 15 splitters)")
     if ops is None:
         ops = CudaOps(keys.device)
-    n_local = int(keys.shape[0])
+    tail = tuple(keys.shape[1:])
+    # one row of kb bytes per key
+    rows = keys.view(torch.uint8).reshape(-1, kb) if keys.numel() else torch.empty((0, kb), dtype=torch.uint8, device=keys.device)
+    n_local = int(rows.shape[0])
+
+    def typed(r):
+        return r.reshape(-1).view(keys.dtype).reshape((-1,) + tail)
 
     if world == 1:
-        ops.local_sort(keys, k, workspace)
-        return ShardedResult(keys, n_local, [n_local], [n_local], np.zeros(0, dtype=ops.to_host(keys[:0]).dtype))
+        ops.local_sort(rows, k, workspace)
+        return ShardedResult(keys, n_local, [n_local], [n_local], np.zeros((0, kb), dtype=np.uint8))
 
     # 1-2. splitters from a global sample
     pos = sample_positions(n_local, samples_per_rank, seed, rank)
-    mine = ops.gather_samples(keys, pos)
-    cnt = torch.tensor([mine.shape[0]], dtype=torch.int64, device=mine.device)
+    mine = ops.gather_samples(rows, pos)
+    cnt = torch.tensor([mine.shape[0]], dtype=torch.int64, device=rows.device)
     cnts = [torch.zeros_like(cnt) for _ in range(world)]
     dist.all_gather(cnts, cnt, group=group)
     sizes = [int(c.item()) for c in cnts]
-    padded = ops.empty_like_n(mine, samples_per_rank)
+    padded = ops.empty_rows(samples_per_rank, kb)
     padded[: mine.shape[0]] = mine
     gathered = [torch.empty_like(padded) for _ in range(world)]
     dist.all_gather(gathered, padded, group=group)
     allsamp = torch.cat([g[:s] for g, s in zip(gathered, sizes)], dim=0).contiguous()
     ops.local_sort(allsamp, k)
     samp_host = ops.to_host(allsamp)
-    splitters = choose_splitters(samp_host, world)
-    if len(splitters) != world - 1:  # no keys anywhere
-        return ShardedResult(keys[:0], 0, [0] * world, [0] * world, samp_host[:0])
-    splitters = np.ascontiguousarray(np.stack(splitters)) if samp_host.ndim > 1 else np.array(splitters, dtype=samp_host.dtype)
+    picks = choose_splitters(samp_host, world)
+    if len(picks) != world - 1:  # no keys anywhere
+        return ShardedResult(keys[:0], 0, [0] * world, [0] * world, np.zeros((0, kb), dtype=np.uint8))
+    splitters = np.ascontiguousarray(np.stack(picks))
 
     # 3. K7: partition by destination rank
-    if send_buffer is None or send_buffer.shape[0] < n_local:
-        send_buffer = ops.empty_like_n(keys, n_local)
-    send = send_buffer[:n_local]
-    counts = ops.partition(keys, send, k, splitters, workspace)
+    if send_buffer is None or send_buffer.numel() * send_buffer.element_size() < n_local * kb:
+        send = ops.empty_rows(n_local, kb)
+    else:
+        send = send_buffer.view(torch.uint8).reshape(-1)[: n_local * kb].reshape(n_local, kb)
+    counts = ops.partition(rows, send, k, splitters, workspace)
 
     # 4. count matrix
-    rows = [torch.zeros_like(counts) for _ in range(world)]
-    dist.all_gather(rows, counts, group=group)
-    cm = np.stack([ops.to_host(r) for r in rows])
+    rws = [torch.zeros_like(counts) for _ in range(world)]
+    dist.all_gather(rws, counts, group=group)
+    cm = np.stack([ops.to_host(r) for r in rws])
     send_counts, recv_counts = exchange_plan(cm, rank)
     n_out = sum(recv_counts)
 
-    # 5. all-to-all (rows of 128-bit keys are 2 x uint64: split sizes count rows)
-    recv = ops.empty_like_n(keys, n_out)
+    # 5. all-to-all: split sizes count rows (= keys)
+    recv = ops.empty_rows(n_out, kb)
     dist.all_to_all_single(recv, send, output_split_sizes=recv_counts, input_split_sizes=send_counts, group=group)
 
     # 6. local LSD sort of the received range
     ops.local_sort(recv, k, workspace)
-    return ShardedResult(recv, n_out, send_counts, recv_counts, splitters)
+    return ShardedResult(typed(recv), n_out, send_counts, recv_counts, splitters)

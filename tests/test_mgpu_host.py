@@ -22,30 +22,32 @@ from radix_sort_b200.api import Kind  # noqa: E402
 
 
 class NumpyOps:
-    """Test double for mgpu.CudaOps on CPU tensors (u64 keys only)."""
+    """Test double for mgpu.CudaOps on CPU tensors: rows of 8 bytes = u64 keys."""
 
-    def gather_samples(self, keys, positions):
-        return keys[torch.from_numpy(positions)].contiguous()
+    @staticmethod
+    def _u64(rows):
+        return rows.numpy().reshape(-1).view(np.uint64)
 
-    def empty_like_n(self, keys, n):
-        return torch.empty((n,) + tuple(keys.shape[1:]), dtype=keys.dtype)
+    def gather_samples(self, rows, positions):
+        return rows[torch.from_numpy(positions)].contiguous()
 
-    def local_sort(self, keys, kind, workspace=None):
-        a = keys.numpy().view(np.uint64)
+    def empty_rows(self, n, key_bytes):
+        return torch.empty((n, key_bytes), dtype=torch.uint8)
+
+    def local_sort(self, rows, kind, workspace=None):
+        a = self._u64(rows)
         a[...] = np.sort(a, kind="stable")
 
-    def partition(self, keys, out, kind, splitters_host, workspace=None):
-        a = keys.numpy().view(np.uint64)
-        dest = np.searchsorted(splitters_host.view(np.uint64), a, side="right")  # #{j : spl[j] <= key}
+    def partition(self, rows, out, kind, splitters_host, workspace=None):
+        a = self._u64(rows)
+        spl = splitters_host.reshape(-1).view(np.uint64)
+        dest = np.searchsorted(spl, a, side="right")  # #{j : spl[j] <= key}
         order = np.argsort(dest, kind="stable")
-        out.numpy().view(np.uint64)[...] = a[order]
-        return torch.from_numpy(np.bincount(dest, minlength=len(splitters_host) + 1).astype(np.int64))
+        self._u64(out)[...] = a[order]
+        return torch.from_numpy(np.bincount(dest, minlength=len(spl) + 1).astype(np.int64))
 
     def to_host(self, t):
         return t.numpy()
-
-    def from_host(self, a):
-        return torch.from_numpy(a)
 
 
 def _free_port():
@@ -69,7 +71,7 @@ def _worker(rank, world, port, n_per_rank, mode, q):
         else:  # ragged: rank 1 holds nothing
             a = rng.integers(0, 2**63, size=n_per_rank if rank == 0 else 0, dtype=np.int64)
         keys = torch.from_numpy(a.copy())
-        # uint64 keys travel as int64 tensors (gloo has no uint64); values < 2^63 keep the order
+        # int64 tensor holding u64 bit patterns < 2^63 (same order either way)
         res = mgpu.sort_sharded(keys, Kind.U64, ops=NumpyOps(), samples_per_rank=512)
         out = res.keys.numpy().copy()
         q.put((rank, a, out, res.send_counts, res.recv_counts))
