@@ -39,7 +39,7 @@ def _fingerprint() -> str:
     for f in files:
         path = f if os.path.isabs(f) else os.path.join(CSRC, f)
         if os.path.isfile(path):
-            h.update(path.encode())
+            h.update(os.path.basename(path).encode())  # names, not absolute paths: the tree moves (gpurun)
             with open(path, "rb") as fh:
                 h.update(fh.read())
     h.update(" ".join(NVCC_FLAGS).encode())
@@ -72,7 +72,7 @@ def build(force: bool = False, verbose: bool = False, jobs: int | None = None) -
     if not force and not needs_build():
         return LIB
     nvcc = _nvcc()
-    objdir = os.path.join(PKG, "build")
+    objdir = os.path.join(PKG, "build") if verbose else os.path.join(PKG, f"build.{os.getpid()}")
     os.makedirs(objdir, exist_ok=True)
     jobs = jobs or int(os.environ.get("B200SORT_BUILD_JOBS", "0")) or max(1, len(os.sched_getaffinity(0)))
     units = translation_units()
@@ -102,8 +102,11 @@ def build(force: bool = False, verbose: bool = False, jobs: int | None = None) -
     if verbose:
         with open(os.path.join(objdir, "ptxas.log"), "w") as fh:
             fh.write("\n".join(log))
-    subprocess.run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs], check=True)
-    shutil.rmtree(objdir, ignore_errors=not verbose) if not verbose else None
+    tmp_lib = LIB + f".tmp{os.getpid()}"
+    subprocess.run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", tmp_lib, *objs], check=True)
+    os.replace(tmp_lib, LIB)  # atomic: concurrent ranks never see a half-written library
+    if not verbose:
+        shutil.rmtree(objdir, ignore_errors=True)
     with open(STAMP, "w") as fh:
         fh.write(_fingerprint())
     return LIB
