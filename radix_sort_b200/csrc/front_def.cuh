@@ -77,7 +77,7 @@ int sort_front(const SortCall& c) {
     if (variant < 0 || variant >= num_variants<FAM, W>()) variant = 0;
     // the TMA ring of the persistent kernel needs 16-byte aligned tiles
     const bool aligned16 = ((uintptr_t)d_elems % 16) == 0 && (!c.alt_out || ((uintptr_t)c.alt_out % 16) == 0);
-    if (Variants<FAM, W>::v[variant].kernel == 1 && !aligned16) variant = Variants<FAM, W>::FALLBACK;
+    if (Variants<FAM, W>::v[variant].kernel >= 1 && !aligned16) variant = Variants<FAM, W>::FALLBACK;
     const VariantDesc vd = Variants<FAM, W>::v[variant];
     const int tile = vd.threads * vd.items;
     const Layout L = make_layout(n, W, D, tile);
@@ -103,7 +103,7 @@ int sort_front(const SortCall& c) {
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        constexpr int HT = 512;
+        constexpr int HT = HistCfg<Tr>::THREADS;
         constexpr size_t HS = HistCfg<Tr>::SMEM;
         auto hk = hist_all_digits_kernel<Tr, HT>;
         static std::atomic<unsigned> configured{0};  // bit per device
@@ -111,7 +111,7 @@ int sort_front(const SortCall& c) {
             B200_CU(cudaFuncSetAttribute(hk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HS));
             configured.fetch_or(1u << (dev & 31), std::memory_order_release);
         }
-        const size_t per_sm = std::max<size_t>(1, std::min<size_t>(4, (220 * 1024) / HS));
+        const size_t per_sm = std::max<size_t>(1, std::min<size_t>(2048 / HT, (220 * 1024) / HS));
         const size_t vecs = (n * W + 15) / 16;
         size_t blocks = (vecs + (size_t)HT * 4 - 1) / ((size_t)HT * 4);
         const size_t cap = (size_t)sms * per_sm;

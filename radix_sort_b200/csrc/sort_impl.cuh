@@ -17,6 +17,7 @@
 
 #include "../../include/b200sort.h"
 #include "sort_kernels.cuh"
+#include "ring_kernel.cuh"
 
 namespace b200 {
 
@@ -45,7 +46,8 @@ template <> struct FamilyTraits<FAM_RECORDS, 16> { using type = RecordTraits<u12
 
 // ---- K3 variants ------------------------------------------------------------------
 // kernel: 0 = onesweep_pass_kernel (one tile per CTA, any alignment)
-//         1 = onesweep_persistent_kernel (TMA ring; 16-byte aligned buffers)
+//         1 = onesweep_persistent_kernel (two-slot TMA ring, look-back warps; 16-byte aligned buffers)
+//         2 = onesweep_ring_kernel (three-slot TMA ring, deferred write-out; ring_kernel.cuh)
 // Index 0 of a table is the default (the fastest measured on B200, profiles/);
 // FALLBACK names the one-tile variant used when a buffer is not 16-byte aligned.  The other entries exist
 // for on-GPU sweeps (b200sort_set_variant).  The counts are repeated as macros
@@ -57,10 +59,10 @@ template <int FAM, int W> struct Variants;
 template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}, {1, 448, 32, 2, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_2 2
 template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}, {1, 448, 24, 2, 64}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_KEYS_4 8
-template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 22, 2, 0}, {1, 448, 16, 2, 64}, {1, 512, 16, 2, 64}, {1, 384, 20, 2, 128}, {1, 448, 20, 2, 64}, {1, 384, 22, 2, 64}, {1, 384, 16, 3, 64}, {1, 384, 16, 2, 128}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_KEYS_8 8
-template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {1, 448, 8, 2, 64}, {1, 384, 12, 2, 128}, {1, 448, 10, 2, 64}, {1, 448, 12, 2, 64}, {1, 384, 12, 2, 64}, {1, 384, 8, 3, 64}, {1, 384, 10, 2, 128}}; static constexpr int FALLBACK = 0; };
+#define B200_NV_KEYS_4 6
+template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 22, 2, 0}, {0, 384, 28, 2, 0}, {0, 512, 16, 2, 0}, {0, 384, 18, 3, 0}, {1, 384, 20, 2, 128}, {2, 384, 16, 2, 128}}; static constexpr int FALLBACK = 0; };
+#define B200_NV_KEYS_8 6
+template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {0, 384, 20, 2, 0}, {0, 512, 12, 2, 0}, {0, 384, 12, 3, 0}, {1, 384, 12, 2, 128}, {2, 384, 10, 2, 128}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_16 3
 template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {1, 256, 8, 3, 64}, {1, 448, 5, 2, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_RECORDS_8 3
@@ -90,9 +92,10 @@ struct VariantEntry {
 template <typename Tr, int KERNEL, int THREADS, int ITEMS, int MINB, int LBT>
 struct PassLauncher {
     using SM = PassSmem<Tr, THREADS, ITEMS>;
-    static constexpr size_t SMEM = KERNEL == 1 ? SM::TOTAL_PERSISTENT : SM::TOTAL;
+    static constexpr size_t SMEM = KERNEL == 2 ? RingSmem<Tr, THREADS, ITEMS>::TOTAL : KERNEL == 1 ? SM::TOTAL_PERSISTENT : SM::TOTAL;
     static auto kernel() {
-        if constexpr (KERNEL == 1) return onesweep_persistent_kernel<Tr, THREADS, ITEMS, LBT, MINB>;
+        if constexpr (KERNEL == 2) return onesweep_ring_kernel<Tr, THREADS, ITEMS, LBT, MINB>;
+        else if constexpr (KERNEL == 1) return onesweep_persistent_kernel<Tr, THREADS, ITEMS, LBT, MINB>;
         else return onesweep_pass_kernel<Tr, THREADS, ITEMS, MINB>;
     }
     // per-device one-time setup: opt in to the dynamic shared memory, read the occupancy
@@ -123,7 +126,7 @@ struct PassLauncher {
         cudaError_t e = prepare(&resident);
         if (e != cudaSuccess) return e;
         unsigned grid = a.num_tiles;
-        if (KERNEL == 1 && grid > (unsigned)resident) grid = (unsigned)resident;
+        if (KERNEL >= 1 && grid > (unsigned)resident) grid = (unsigned)resident;
         kernel()<<<grid, THREADS + LBT, SMEM, st>>>(a);
         count_launch();
         return cudaGetLastError();

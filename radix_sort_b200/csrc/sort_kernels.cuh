@@ -69,14 +69,18 @@ __device__ __forceinline__ u128 ld_elem<u128>(const u128* p) {
 // is not slowed by same-address lanes (the unit merges them), so skewed inputs
 // need no software warp aggregation -- the ballot/branch version of this kernel
 // spent 68 instructions per 32 keys for 21 % of HBM peak.  What does cost is bank
-// conflicts between DIFFERENT digits (3.2 wavefronts per atomic with one table),
-// so every bin is replicated R times with the copy chosen by lane % R: lanes
-// l, l+R, ... collide only if their digits are congruent mod 32/R.
+// conflicts between DIFFERENT digits: with 8 copies per bin the kernel ran the
+// SM's LSU data pipe at 96 % (ncu, 3.0 wavefronts per atomic) for 2.6 TB/s.  So
+// every bin has R copies, the copy chosen by lane % R, with R as large as 128 KB
+// of shared memory allows: R = 32 (keys of <= 4 bytes) puts lane l on bank l for
+// every digit -- one wavefront per atomic, no conflicts at all; R = 16 (8-byte
+// keys) leaves one possible partner lane, R = 8 (16-byte keys) three.
 // ---------------------------------------------------------------------------
 template <typename Tr>
 struct HistCfg {
-    static constexpr int R = Tr::DIGITS <= 8 ? 8 : 4;
+    static constexpr int R = Tr::DIGITS <= 4 ? 32 : Tr::DIGITS <= 8 ? 16 : 8;
     static constexpr size_t SMEM = (size_t)Tr::DIGITS * RADIX * R * sizeof(uint32_t);
+    static constexpr int THREADS = 1024;
 };
 
 template <typename Tr, int THREADS>
@@ -131,7 +135,7 @@ hist_all_digits_kernel(const typename Tr::elem_t* __restrict__ in, size_t n,
     for (int k = tid; k < D * RADIX; k += THREADS) {
         uint32_t c = 0;
 #pragma unroll
-        for (int r = 0; r < R; ++r) c += hist_sh[k * R + r];
+        for (int r = 0; r < R; ++r) c += hist_sh[k * R + ((r + tid) & (R - 1))];  // rotated: lanes read distinct banks
         if (c) atomicAdd(&hist[k], (unsigned long long)c);
     }
 }
@@ -272,6 +276,7 @@ struct PassShared {
     uint32_t* cnt;                  // [256] keys of the tile with this digit
     uint32_t* misc;                 // [0..1] tickets, [2..9] warp totals of the digit scan
     unsigned long long* mbar;       // [2] mbarriers of the ring (persistent kernel)
+    __device__ __forceinline__ PassShared() {}
     __device__ __forceinline__ PassShared(unsigned char* raw, size_t tile_bytes_total) {
         tile = reinterpret_cast<typename Tr::elem_t*>(raw);
         unsigned char* aux = raw + tile_bytes_total;
@@ -418,14 +423,13 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
 // construction) from the keys still in global memory, and rewrite its slots.
 // Entered by a whole CTA; warp_hist may hold anything; excl/gptr are valid.
 template <typename Tr, int THREADS, int ITEMS, int LBT>
-__device__ __noinline__ void rerank_tile(typename Tr::elem_t* tile_buf, unsigned char* aux_minus_tiles, size_t tile_bytes_total,
+__device__ __noinline__ void rerank_tile(const PassShared<Tr, THREADS, ITEMS>* shp,
                                          const PassArgs<Tr>* ap, const typename Tr::elem_t* src_tile,
                                          uint32_t tile_n, uint32_t xf_in, uint32_t xf_out) {
     using E = typename Tr::elem_t;
     constexpr int WARPS = THREADS / 32;
     const PassArgs<Tr>& a = *ap;
-    PassShared<Tr, THREADS, ITEMS> sh(aux_minus_tiles, tile_bytes_total);
-    sh.tile = tile_buf;
+    const PassShared<Tr, THREADS, ITEMS> sh = *shp;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lane_lt = (1u << lane) - 1u;
     const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
@@ -649,6 +653,9 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     constexpr int TILE = THREADS * ITEMS;
     static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit needed");
 
+    // the ticket and the pass plan are two independent round trips to L2: ask for both at once
+    uint32_t ticket = 0;
+    if (threadIdx.x == 0) ticket = atomicAdd(a.ticket, 1u);
     const PassPlan pp = a.plan->pass[a.pass];
     if (pp.skip) return;
 
@@ -660,8 +667,11 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     E* __restrict__ dst = pp.src_is_tmp ? a.keys : a.tmp;
 
     // tile id from a ticket, not blockIdx: every predecessor a tile may wait on
-    // in the look-back has already started, whatever order CTAs are dispatched in
-    if (tid == 0) sh.misc[0] = atomicAdd(a.ticket, 1u);
+    // in the look-back has already started, whatever order CTAs are dispatched in.
+    // (Requesting the keys of tile blockIdx.x before the ticket is known was tried:
+    // tickets and block ids disagree often enough that the re-loads cost more than
+    // the hidden round trip -- r01 sweep v7.)
+    if (tid == 0) sh.misc[0] = ticket;
 #pragma unroll
     for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
     __syncthreads();
@@ -684,7 +694,7 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     if (Tr::NEEDS_STABLE || a.pass == 0) return;
     if (!__syncthreads_or(bad)) return;
     if (tid == 0) atomicAdd(a.stats, 1u);
-    rerank_tile<Tr, THREADS, ITEMS, 0>(sh.tile, smem_raw, SM::TILE_BYTES, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
+    rerank_tile<Tr, THREADS, ITEMS, 0>(&sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
 }
 
 // ---- TMA bulk copy + mbarrier (sm_90+ PTX; SASS: UBLKCP / SYNCS) ------------------
@@ -806,7 +816,7 @@ onesweep_persistent_kernel(const __grid_constant__ PassArgs<Tr> a) {
         fence_proxy_async();  // generic-proxy accesses of this slot before the next bulk copy into it
         if (workers_sync_or<WORKERS, LBT>(bad)) {
             if (tid == 0) atomicAdd(a.stats, 1u);
-            rerank_tile<Tr, WORKERS, ITEMS, LBT>(sh.tile, smem_raw, 2 * SM::TILE_BYTES, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
+            rerank_tile<Tr, WORKERS, ITEMS, LBT>(&sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
             for (int i = tid; i < WARPS * RADIX; i += WORKERS) sh.warp_hist[i] = 0;
             fence_proxy_async();
             workers_sync<WORKERS, LBT>();
