@@ -119,12 +119,22 @@ hist_all_digits_kernel(const typename Tr::elem_t* __restrict__ in, size_t n,
 
     const size_t stride = (size_t)gridDim.x * THREADS;
     size_t i = (size_t)blockIdx.x * THREADS + tid;
-    for (; i + 3 * stride < nvec; i += 4 * stride) {
-        const uint4 a = __ldg(vec + i);
-        const uint4 b = __ldg(vec + i + stride);
-        const uint4 c = __ldg(vec + i + 2 * stride);
-        const uint4 d = __ldg(vec + i + 3 * stride);
-        count_vec(a); count_vec(b); count_vec(c); count_vec(d);
+    // software pipeline: the four vectors of the next round are requested before
+    // the current four are counted, so HBM and the atomic unit work at the same time
+    if (i + 3 * stride < nvec) {
+        uint4 a = __ldg(vec + i), b = __ldg(vec + i + stride), c = __ldg(vec + i + 2 * stride), d = __ldg(vec + i + 3 * stride);
+        for (;;) {
+            const size_t ni = i + 4 * stride;
+            const bool more = ni + 3 * stride < nvec;
+            uint4 na, nb, nc, nd;
+            if (more) {
+                na = __ldg(vec + ni); nb = __ldg(vec + ni + stride); nc = __ldg(vec + ni + 2 * stride); nd = __ldg(vec + ni + 3 * stride);
+            }
+            count_vec(a); count_vec(b); count_vec(c); count_vec(d);
+            i = ni;
+            if (!more) break;
+            a = na; b = nb; c = nc; d = nd;
+        }
     }
     for (; i < nvec; i += stride) count_vec(__ldg(vec + i));
     if (blockIdx.x == 0) {
