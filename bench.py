@@ -8,7 +8,8 @@ A step = one full sort of the workload.  N = 1: BASELINE.json configs[1],
 1 000 000 000 uniform random u64 keys resident in HBM (b200sort_keys_device).
 N > 1 (launched under torchrun, one rank per GPU): the same 1e9 u64 keys PER
 GPU, sharded (weak scaling; the shape of configs[4]): sample -> splitters ->
-K7 partition -> NCCL all-to-all -> local LSD sort (radix_sort_b200/mgpu.py).
+K7 partition fused with the exchange (peer stores over NVLink; NCCL all-to-all as
+fallback) -> local LSD sort (radix_sort_b200/mgpu.py).
 Every step starts from the same unsorted input (restored by a device copy
 outside the timed region); the timed region of a step is bracketed by CUDA
 events on the launching stream; rank time = sum over steps, job time = max
@@ -192,8 +193,22 @@ def run_gpu(args):
     distr.generate(pristine, K, distr.Distr.UNIFORM, 0, seed=SEED, index_base=rank * n)
     keys = torch.empty_like(pristine)
     ws = torch.empty(rs.temp_bytes(int(n * 1.25) + 1024, K), dtype=torch.uint8, device=dev)
-    sendbuf = torch.empty_like(pristine) if world > 1 else None
     fp_in = verify.fingerprint(pristine, K)
+    # N > 1: fused K7 + exchange over peer memory (torch symmetric memory) unless
+    # it cannot be set up here; then the NCCL all-to-all path, and the line says so
+    exchange, exchange_note, sendbuf = None, "single GPU", None
+    if world > 1:
+        exchange_note = "nccl all_to_all_single"
+        if args.exchange in ("auto", "fused"):
+            try:
+                exchange = mgpu.PeerExchange(int(n * 1.25) + 1024, KEY_BYTES, dev)
+                exchange_note = "fused: K7 stores into peer receive buffers over NVLink (symmetric memory)"
+            except Exception as e:  # noqa: BLE001
+                if args.exchange == "fused":
+                    raise
+                exchange_note = f"nccl all_to_all_single (peer memory unavailable: {type(e).__name__}: {str(e)[:120]})"
+        if exchange is None:
+            sendbuf = torch.empty_like(pristine)
 
     def barrier():
         if dist is not None:
@@ -210,7 +225,7 @@ def run_gpu(args):
             rs.radix_sort(keys, K, workspace=ws)
             out = keys
         else:
-            out = mgpu.sort_sharded(keys, K, workspace=ws, send_buffer=sendbuf).keys
+            out = mgpu.sort_sharded(keys, K, workspace=ws, send_buffer=sendbuf, exchange=exchange).keys
         e1.record()
         torch.cuda.synchronize()
         return e0.elapsed_time(e1), out
@@ -230,6 +245,12 @@ def run_gpu(args):
     barrier()
     launches = rs.launch_count() - launches0
     clocks = sampler.stop() if rank == 0 else None
+    phases = {}
+    if world > 1:  # one extra, untimed step with per-phase device timings
+        keys.copy_(pristine)
+        barrier()
+        out = mgpu.sort_sharded(keys, K, workspace=ws, send_buffer=sendbuf, exchange=exchange, timings=phases).keys
+        barrier()
 
     # correctness of the last timed step: sorted + same multiset <=> bit-identical to the reference's output
     unsorted = verify.count_unsorted(out, K)
@@ -307,7 +328,7 @@ def run_gpu(args):
             _ffi.check(rc)
         else:
             keys.copy_(host[:n], non_blocking=True)
-            res = mgpu.sort_sharded(keys, K, workspace=ws, send_buffer=sendbuf)
+            res = mgpu.sort_sharded(keys, K, workspace=ws, send_buffer=sendbuf, exchange=exchange)
             host[: res.n_out].copy_(res.keys, non_blocking=True)
             torch.cuda.synchronize()
             d2h = res.n_out * KEY_BYTES
@@ -341,8 +362,9 @@ def run_gpu(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
         "config": {"workload": ("uniform random u64 keys, 1B elements, single B200 (BASELINE.json configs[1])" if world == 1 else
-                                f"uniform random u64 keys, {n} per GPU x {world} GPUs, sharded; MSD splitters + NCCL all-to-all + local LSD "
+                                f"uniform random u64 keys, {n} per GPU x {world} GPUs, sharded; MSD splitters + exchange + local LSD "
                                 "(weak-scaled form of BASELINE.json configs[4])"),
+                   "exchange": exchange_note, "phases_ms_rank0": {k_: round(v_, 3) for k_, v_ in phases.items()},
                    "keys_per_gpu": n, "seed": SEED, "digits": DIGITS, "digit_bits": 8,
                    "l2": "inputs (8 GB/GPU) exceed the 126 MB L2; no flush between steps",
                    "e2e_steps": e2e_steps, "verified": "sorted + multiset fingerprint == input (bit-identical to the reference's output)"},
@@ -372,6 +394,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--keys", dest="n", type=int, default=N_KEYS, help="keys per GPU (default: the BASELINE.json workload)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "fused", "nccl"],
+                    help="N > 1: fused K7 peer stores, NCCL all-to-all, or fused with fallback (default)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -164,6 +164,32 @@ int b200sort_partition_device(const void *d_in, void *d_out, void *d_tmp, size_t
                               size_t n, int kind, const void *splitters, int nsplit,
                               uint64_t *d_counts, void *stream);
 
+/* K7 fused with the exchange: the same partition, split in two calls around the
+ * caller's count exchange, storing every bucket straight into the receive
+ * buffer of its destination GPU over NVLink (peer memory mapped into this
+ * process: CUDA IPC / symmetric memory; P2P access must be enabled).
+ *
+ *   1. b200sort_partition_count_device: reads the keys once, writes the
+ *      per-destination counts (nsplit + 1 uint64) to d_counts and leaves its
+ *      state in d_tmp.
+ *   2. the caller exchanges the counts (all_gather) and computes, for every
+ *      destination r, the element offset in r's receive buffer at which this
+ *      rank's keys start (= keys sent to r by lower ranks).
+ *   3. b200sort_partition_exchange_device: SAME d_in, d_tmp, n, kind and
+ *      splitters, d_tmp untouched in between.  peer_bases: nsplit + 1 device
+ *      pointers in HOST memory, peer_bases[r] = rank r's receive buffer as
+ *      addressable from this device (own rank: the local buffer).
+ *      d_peer_offsets: nsplit + 1 uint64 element offsets in DEVICE memory.
+ *      Returns when the stores are enqueued; the caller synchronises the
+ *      ranks (barrier after stream completion) before reading receive buffers.
+ * There is no reference counterpart (the reference is single-process); this
+ * replaces the all-to-all of the unfused path (radix_sort_b200/mgpu.py). */
+int b200sort_partition_count_device(const void *d_in, void *d_tmp, size_t tmp_bytes, size_t n, int kind,
+                                    const void *splitters, int nsplit, uint64_t *d_counts, void *stream);
+int b200sort_partition_exchange_device(const void *d_in, void *d_tmp, size_t tmp_bytes, size_t n, int kind,
+                                       const void *splitters, int nsplit, void *const *peer_bases,
+                                       const uint64_t *d_peer_offsets, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -34,6 +34,10 @@ PROTOTYPES = {
     "b200sort_count_unsorted": (c_int, [c_void_p, c_size_t, c_int, c_void_p, c_void_p]),
     "b200sort_partition_device": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_size_t, c_int, c_void_p, c_int,
                                           c_void_p, c_void_p]),
+    "b200sort_partition_count_device": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_int, c_void_p, c_int,
+                                                c_void_p, c_void_p]),
+    "b200sort_partition_exchange_device": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_int, c_void_p, c_int,
+                                                   c_void_p, c_void_p, c_void_p]),
 }
 
 _lib = None

@@ -281,6 +281,44 @@ int b200sort_partition_device(const void* d_in, void* d_out, void* d_tmp, size_t
     return front_by_width<FAM_PARTITION>(kb, c);
 }
 
+static int partition_phase(int phase, const void* d_in, void* d_tmp, size_t tmp_bytes, size_t n, int kind,
+                           const void* splitters, int nsplit, uint64_t* d_counts, void* const* peer_bases,
+                           const uint64_t* d_peer_offsets, void* stream) {
+    if (nsplit < 0 || nsplit > MAX_SPLITTERS) return fail(B200SORT_ERR_INVALID_ARG, "nsplit must be in [0, 15]");
+    if (nsplit > 0 && !splitters) return fail(B200SORT_ERR_INVALID_ARG, "null splitters");
+    if (n && !d_in) return fail(B200SORT_ERR_INVALID_ARG, "null device pointer");
+    if (phase == SortCall::PHASE_COUNT && !d_counts) return fail(B200SORT_ERR_INVALID_ARG, "null d_counts");
+    if (phase == SortCall::PHASE_SCATTER && (!peer_bases || !d_peer_offsets))
+        return fail(B200SORT_ERR_INVALID_ARG, "null peer_bases / d_peer_offsets");
+    const size_t kb = b200sort_key_bytes(kind);
+    if (kb == 0) return fail(B200SORT_ERR_UNSUPPORTED_KIND, "unknown key kind " + std::to_string(kind));
+    SortCall c;
+    c.elems = const_cast<void*>(d_in); c.ws = d_tmp; c.ws_bytes = tmp_bytes; c.n = n;
+    // every bucket has its own base (peer_bases); alt_out only has to be non-null so
+    // that the front treats the call as single-pass with no copy-back
+    c.alt_out = phase == SortCall::PHASE_SCATTER ? peer_bases[0] : const_cast<void*>(d_in);
+    c.st = static_cast<cudaStream_t>(stream); c.flags = B200SORT_FLAG_NO_SKIP; c.xf = kind_xf(kind);
+    if (phase == SortCall::PHASE_COUNT) {
+        c.hist_copy = reinterpret_cast<unsigned long long*>(d_counts); c.hist_copy_words = nsplit + 1;
+    }
+    c.splitters = splitters; c.nsplit = nsplit; c.phase = phase;
+    c.peer_bases = peer_bases; c.peer_offsets = reinterpret_cast<const unsigned long long*>(d_peer_offsets);
+    return front_by_width<FAM_PARTITION>(kb, c);
+}
+
+int b200sort_partition_count_device(const void* d_in, void* d_tmp, size_t tmp_bytes, size_t n, int kind,
+                                    const void* splitters, int nsplit, uint64_t* d_counts, void* stream) {
+    return partition_phase(SortCall::PHASE_COUNT, d_in, d_tmp, tmp_bytes, n, kind, splitters, nsplit, d_counts, nullptr,
+                           nullptr, stream);
+}
+
+int b200sort_partition_exchange_device(const void* d_in, void* d_tmp, size_t tmp_bytes, size_t n, int kind,
+                                       const void* splitters, int nsplit, void* const* peer_bases,
+                                       const uint64_t* d_peer_offsets, void* stream) {
+    return partition_phase(SortCall::PHASE_SCATTER, d_in, d_tmp, tmp_bytes, n, kind, splitters, nsplit, nullptr,
+                           peer_bases, d_peer_offsets, stream);
+}
+
 unsigned long long b200sort_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 int b200sort_set_variant(int key_bytes, int variant) {

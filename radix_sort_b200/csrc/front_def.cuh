@@ -48,6 +48,12 @@ int make_params(const SortCall& c, typename FamilyTraits<FAM, W>::type::Params* 
         for (int j = 0; j < c.nsplit; ++j) p.spl[j] = to_ordered_rt<U>(raw[j], c.xf);
         for (int j = 1; j < c.nsplit; ++j)
             if (ordered_less<U>(p.spl[j], p.spl[j - 1])) return fail(B200SORT_ERR_INVALID_ARG, "splitters are not ascending");
+        if (c.peer_bases)
+            for (int j = 0; j <= c.nsplit; ++j) {
+                if (!c.peer_bases[j] || ((uintptr_t)c.peer_bases[j] % alignof(U)) != 0)
+                    return fail(B200SORT_ERR_INVALID_ARG, "peer buffer null or not aligned to the element size");
+                p.peer[j] = (unsigned long long)(uintptr_t)c.peer_bases[j];
+            }
     }
     *prm = p;
     return B200SORT_OK;
@@ -63,8 +69,10 @@ int sort_front(const SortCall& c) {
     cudaStream_t st = c.st;
     typename Tr::Params prm;
     if (int rc = make_params<FAM, W>(c, &prm)) return rc;
+    const bool do_count = c.phase != SortCall::PHASE_SCATTER;
+    const bool do_scatter = c.phase != SortCall::PHASE_COUNT;
     if (n == 0) {
-        if (c.hist_copy) B200_CU(cudaMemsetAsync(c.hist_copy, 0, (size_t)c.hist_copy_words * 8, st));
+        if (c.hist_copy && do_count) B200_CU(cudaMemsetAsync(c.hist_copy, 0, (size_t)c.hist_copy_words * 8, st));
         return B200SORT_OK;
     }
     E* d_elems = static_cast<E*>(c.elems);
@@ -77,7 +85,7 @@ int sort_front(const SortCall& c) {
     if (variant < 0 || variant >= num_variants<FAM, W>()) variant = 0;
     // the TMA ring of the persistent kernel needs 16-byte aligned tiles
     const bool aligned16 = ((uintptr_t)d_elems % 16) == 0 && (!c.alt_out || ((uintptr_t)c.alt_out % 16) == 0);
-    if (Variants<FAM, W>::v[variant].kernel >= 1 && !aligned16) variant = Variants<FAM, W>::FALLBACK;
+    if ((Variants<FAM, W>::v[variant].kernel == 1 || Variants<FAM, W>::v[variant].kernel == 2) && !aligned16) variant = Variants<FAM, W>::FALLBACK;
     const VariantDesc vd = Variants<FAM, W>::v[variant];
     const int tile = vd.threads * vd.items;
     const Layout L = make_layout(n, W, D, tile);
@@ -96,10 +104,10 @@ int sort_front(const SortCall& c) {
 
     PhaseTimer timer(c.out_ms != nullptr, st);
     timer.mark();
-    B200_CU(cudaMemsetAsync(ws + L.zero_off, 0, L.zero_bytes, st));
+    if (do_count) B200_CU(cudaMemsetAsync(ws + L.zero_off, 0, L.zero_bytes, st));
 
     // K1: one read, all digit histograms
-    {
+    if (do_count) {
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -122,14 +130,20 @@ int sort_front(const SortCall& c) {
         B200_CU(cudaGetLastError());
     }
     timer.mark();
-    if (c.hist_copy)
-        B200_CU(cudaMemcpyAsync(c.hist_copy, hist, (size_t)c.hist_copy_words * 8, cudaMemcpyDeviceToDevice, st));
-    // K2: bucket bases + pass plan
-    scan_plan_kernel<<<1, RADIX, 0, st>>>(hist, bins, plan, (unsigned long long)n, D, L.portions,
-                                          (c.flags & B200SORT_FLAG_NO_SKIP) ? 1 : 0);
-    count_launch();
-    B200_CU(cudaGetLastError());
+    if (do_count) {
+        if (c.hist_copy)
+            B200_CU(cudaMemcpyAsync(c.hist_copy, hist, (size_t)c.hist_copy_words * 8, cudaMemcpyDeviceToDevice, st));
+        // K2: bucket bases + pass plan
+        scan_plan_kernel<<<1, RADIX, 0, st>>>(hist, bins, plan, (unsigned long long)n, D, L.portions,
+                                              (c.flags & B200SORT_FLAG_NO_SKIP) ? 1 : 0);
+        count_launch();
+        B200_CU(cudaGetLastError());
+    }
     timer.mark();
+    if (!do_scatter) return B200SORT_OK;
+    // fused exchange: bucket r starts at element peer_offsets[r] of rank r's receive buffer
+    if (c.peer_offsets)
+        B200_CU(cudaMemcpyAsync(bins, c.peer_offsets, (size_t)(c.nsplit + 1) * 8, cudaMemcpyDeviceToDevice, st));
 
     // K3: one launch per digit per portion
     size_t lb_cursor = 0;

@@ -157,11 +157,14 @@ struct KeyTraits {
     // equal keys are bit-identical, so a pass only has to keep same-digit keys in
     // the order of their lower digits -- which K3 can check exactly (sort_kernels.cuh)
     static constexpr bool NEEDS_STABLE = false;
+    static constexpr bool FEW_BUCKETS = false;
     struct Params { int xf; };
     __device__ __forceinline__ static bool prefix_less(elem_t a, elem_t b, int pass, const Params&) { return b200::prefix_less<U>(a, b, pass); }
     __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params& p) { return to_ordered_rt<U>(e, p.xf); }
     __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params& p) { return from_ordered_rt<U>(e, p.xf); }
     __device__ __forceinline__ static unsigned digit(elem_t e, int pass, const Params&) { return digit_of<U>(e, pass); }
+    // byte address of element 0 of the buffer bucket d is written to
+    __device__ __forceinline__ static unsigned long long dst_base(unsigned, const void* dst, const Params&) { return (unsigned long long)dst; }
 };
 
 // Partition traits (multi-GPU MSD step): one "pass" whose digit is the
@@ -175,10 +178,17 @@ struct PartitionTraits {
     static constexpr int KEY_BYTES = (int)sizeof(U);
     static constexpr int DIGITS = 1;
     static constexpr bool NEEDS_STABLE = false;  // order inside a destination is irrelevant: it is sorted next
+    // at most 16 buckets and a digit that costs 15 wide compares: K3 computes it once
+    // per key (4-bit codes kept in registers) and writes the tile out bucket by bucket
+    static constexpr bool FEW_BUCKETS = true;
     struct Params {
         U spl[MAX_SPLITTERS];
         int nsplit;
         int xf;
+        // fused exchange: peer[r] != 0 is the receive buffer of rank r as mapped into
+        // this process (peer memory over NVLink); bucket r is then stored there
+        // directly and bins_in[r] counts elements from the start of THAT buffer
+        unsigned long long peer[MAX_SPLITTERS + 1];
     };
     __device__ __forceinline__ static bool prefix_less(elem_t, elem_t, int, const Params&) { return false; }
     __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params&) { return e; }
@@ -186,10 +196,15 @@ struct PartitionTraits {
     __device__ __forceinline__ static unsigned digit(elem_t e, int, const Params& p) {
         const U k = to_ordered_rt<U>(e, p.xf);
         unsigned r = 0;
-#pragma unroll
-        for (int j = 0; j < MAX_SPLITTERS; ++j)
-            if (j < p.nsplit && !ordered_less<U>(k, p.spl[j])) ++r;
+        // warp-uniform trip count: 2 GPUs cost one compare per key, not fifteen
+#pragma unroll 1
+        for (int j = 0; j < p.nsplit; ++j)
+            if (!ordered_less<U>(k, p.spl[j])) ++r;
         return r;
+    }
+    __device__ __forceinline__ static unsigned long long dst_base(unsigned d, const void* dst, const Params& p) {
+        const unsigned long long peer = d <= (unsigned)MAX_SPLITTERS ? p.peer[d] : 0ull;
+        return peer ? peer : (unsigned long long)dst;
     }
 };
 
@@ -205,6 +220,7 @@ struct RecordTraits<unsigned long long, K> {  // 8-byte record, 4-byte key
     static constexpr int KEY_BYTES = (int)sizeof(K);
     static constexpr int DIGITS = (int)sizeof(K);
     static constexpr bool NEEDS_STABLE = true;  // payloads make the order of equal keys observable (tests.rs:175-187)
+    static constexpr bool FEW_BUCKETS = false;
     struct Params { int key_shift; int xf; };
     __device__ __forceinline__ static bool prefix_less(elem_t, elem_t, int, const Params&) { return false; }
     __device__ __forceinline__ static K key(elem_t e, const Params& p) { return (K)(e >> p.key_shift); }
@@ -221,6 +237,7 @@ struct RecordTraits<unsigned long long, K> {  // 8-byte record, 4-byte key
     __device__ __forceinline__ static unsigned digit(elem_t e, int pass, const Params& p) {
         return (unsigned)(e >> (p.key_shift + 8 * pass)) & 0xFFu;
     }
+    __device__ __forceinline__ static unsigned long long dst_base(unsigned, const void* dst, const Params&) { return (unsigned long long)dst; }
 };
 
 template <>
@@ -230,6 +247,7 @@ struct RecordTraits<u128, unsigned long long> {  // 16-byte record, 8-byte key
     static constexpr int KEY_BYTES = 8;
     static constexpr int DIGITS = 8;
     static constexpr bool NEEDS_STABLE = true;
+    static constexpr bool FEW_BUCKETS = false;
     struct Params { int key_shift; int xf; };  // key_shift: 0 -> key in .lo, 64 -> key in .hi
     __device__ __forceinline__ static bool prefix_less(elem_t, elem_t, int, const Params&) { return false; }
     __device__ __forceinline__ static key_t key(elem_t e, const Params& p) { return p.key_shift ? e.hi : e.lo; }
@@ -246,6 +264,7 @@ struct RecordTraits<u128, unsigned long long> {  // 16-byte record, 8-byte key
     __device__ __forceinline__ static unsigned digit(elem_t e, int pass, const Params& p) {
         return (unsigned)(key(e, p) >> (8 * pass)) & 0xFFu;
     }
+    __device__ __forceinline__ static unsigned long long dst_base(unsigned, const void* dst, const Params&) { return (unsigned long long)dst; }
 };
 
 }  // namespace b200

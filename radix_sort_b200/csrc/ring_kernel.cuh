@@ -124,7 +124,7 @@ __device__ __forceinline__ void ring_lookback(const PassArgs<Tr>& a, typename Tr
     for (int q = 0; q < NDL; ++q) {
         const int d = q * LBT + ltid;
         const unsigned long long gbase = bin[q] + sum[q];
-        gptr[d] = (unsigned long long)dst + (gbase - excl[d]) * sizeof(E);
+        gptr[d] = Tr::dst_base((unsigned)d, dst, a.prm) + (gbase - excl[d]) * sizeof(E);
         if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[d] = gbase + cnt[d];
     }
     bar_arrive_p<RB_GPTR, WORKERS + LBT>(parity);
@@ -315,7 +315,7 @@ onesweep_ring_kernel(const __grid_constant__ PassArgs<Tr> a) {
         fence_proxy_async();  // generic-proxy accesses of the slot just written out, before the next bulk copy into it
         if (bar_red_or<BAR_WORKERS, WORKERS>(bad)) {
             if (tid == 0) atomicAdd(a.stats, 1u);
-            rerank_tile<Tr, WORKERS, ITEMS, LBT>(&prev, &a, src + (size_t)prev_tile * TILE, prev_n, pp.xf_in, pp.xf_out);
+            rerank_tile<Tr, WORKERS, ITEMS, LBT>(prev, &a, src + (size_t)prev_tile * TILE, prev_n, pp.xf_in, pp.xf_out);
             for (int i = tid; i < WARPS * RADIX; i += WORKERS) warp_hist[i] = 0;
             fence_proxy_async();
             bar_sync<BAR_WORKERS, WORKERS>();
@@ -334,7 +334,7 @@ onesweep_ring_kernel(const __grid_constant__ PassArgs<Tr> a) {
         const bool bad = flush_prev();
         if (bar_red_or<BAR_WORKERS, WORKERS>(bad)) {
             if (tid == 0) atomicAdd(a.stats, 1u);
-            rerank_tile<Tr, WORKERS, ITEMS, LBT>(&prev, &a, src + (size_t)prev_tile * TILE, prev_n, pp.xf_in, pp.xf_out);
+            rerank_tile<Tr, WORKERS, ITEMS, LBT>(prev, &a, src + (size_t)prev_tile * TILE, prev_n, pp.xf_in, pp.xf_out);
         }
     }
 }

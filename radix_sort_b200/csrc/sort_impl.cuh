@@ -18,6 +18,7 @@
 #include "../../include/b200sort.h"
 #include "sort_kernels.cuh"
 #include "ring_kernel.cuh"
+#include "stream_kernel.cuh"
 
 namespace b200 {
 
@@ -48,27 +49,29 @@ template <> struct FamilyTraits<FAM_RECORDS, 16> { using type = RecordTraits<u12
 // kernel: 0 = onesweep_pass_kernel (one tile per CTA, any alignment)
 //         1 = onesweep_persistent_kernel (two-slot TMA ring, look-back warps; 16-byte aligned buffers)
 //         2 = onesweep_ring_kernel (three-slot TMA ring, deferred write-out; ring_kernel.cuh)
+//         3 = onesweep_stream_kernel (resident CTAs, next tile's keys prefetched into the dead
+//             key registers; any alignment; stream_kernel.cuh)
 // Index 0 of a table is the default (the fastest measured on B200, profiles/);
 // FALLBACK names the one-tile variant used when a buffer is not 16-byte aligned.  The other entries exist
 // for on-GPU sweeps (b200sort_set_variant).  The counts are repeated as macros
 // because the dispatcher and the build script need them in the preprocessor.
-struct VariantDesc { int kernel, threads, items, min_blocks, lbt; };  // threads = worker threads; lbt = look-back threads
+struct VariantDesc { int kernel, threads, items, min_blocks, lbt; };  // threads = worker threads; lbt = look-back threads (kernel 0: predecessors read per look-back round, 0 = LB_BATCH)
 
 template <int FAM, int W> struct Variants;
-#define B200_NV_KEYS_1 2
-template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}, {1, 448, 32, 2, 64}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_KEYS_2 2
-template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}, {1, 448, 24, 2, 64}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_KEYS_4 6
-template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 22, 2, 0}, {0, 384, 28, 2, 0}, {0, 512, 16, 2, 0}, {0, 384, 18, 3, 0}, {1, 384, 20, 2, 128}, {2, 384, 16, 2, 128}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_KEYS_8 6
-template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {0, 384, 20, 2, 0}, {0, 512, 12, 2, 0}, {0, 384, 12, 3, 0}, {1, 384, 12, 2, 128}, {2, 384, 10, 2, 128}}; static constexpr int FALLBACK = 0; };
+#define B200_NV_KEYS_1 3
+template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}, {3, 512, 32, 2, 0}, {1, 448, 32, 2, 64}}; static constexpr int FALLBACK = 0; };
+#define B200_NV_KEYS_2 3
+template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}, {3, 512, 24, 2, 0}, {1, 448, 24, 2, 64}}; static constexpr int FALLBACK = 0; };
+#define B200_NV_KEYS_4 5
+template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{3, 512, 22, 2, 0}, {0, 512, 22, 2, 0}, {3, 512, 24, 2, 0}, {1, 384, 20, 2, 128}, {2, 384, 16, 2, 128}}; static constexpr int FALLBACK = 0; };
+#define B200_NV_KEYS_8 5
+template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {3, 512, 16, 2, 0}, {0, 512, 16, 2, 256 * 64}, {1, 384, 12, 2, 128}, {2, 384, 10, 2, 128}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_16 3
-template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {1, 256, 8, 3, 64}, {1, 448, 5, 2, 64}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {3, 256, 12, 2, 0}, {1, 256, 8, 3, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_RECORDS_8 3
-template <> struct Variants<FAM_RECORDS, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0}, {1, 448, 8, 2, 64}, {1, 448, 10, 2, 64}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_RECORDS, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0}, {3, 512, 12, 2, 0}, {1, 448, 8, 2, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_RECORDS_16 3
-template <> struct Variants<FAM_RECORDS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {1, 256, 8, 3, 64}, {1, 448, 5, 2, 64}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_RECORDS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {3, 256, 12, 2, 0}, {1, 256, 8, 3, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_PARTITION_1 1
 template <> struct Variants<FAM_PARTITION, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_PARTITION_2 1
@@ -92,11 +95,14 @@ struct VariantEntry {
 template <typename Tr, int KERNEL, int THREADS, int ITEMS, int MINB, int LBT>
 struct PassLauncher {
     using SM = PassSmem<Tr, THREADS, ITEMS>;
+    static constexpr int BLOCK = THREADS + ((KERNEL == 0 || KERNEL == 3) ? 0 : LBT);  // kernels 0, 3 read lbt as the look-back batch
+    static constexpr int LBB = (LBT & 255) > 0 ? (LBT & 255) : LB_BATCH;
     static constexpr size_t SMEM = KERNEL == 2 ? RingSmem<Tr, THREADS, ITEMS>::TOTAL : KERNEL == 1 ? SM::TOTAL_PERSISTENT : SM::TOTAL;
     static auto kernel() {
-        if constexpr (KERNEL == 2) return onesweep_ring_kernel<Tr, THREADS, ITEMS, LBT, MINB>;
+        if constexpr (KERNEL == 3) return onesweep_stream_kernel<Tr, THREADS, ITEMS, MINB, LBB, (LBT >> 8)>;
+        else if constexpr (KERNEL == 2) return onesweep_ring_kernel<Tr, THREADS, ITEMS, LBT, MINB>;
         else if constexpr (KERNEL == 1) return onesweep_persistent_kernel<Tr, THREADS, ITEMS, LBT, MINB>;
-        else return onesweep_pass_kernel<Tr, THREADS, ITEMS, MINB>;
+        else return onesweep_pass_kernel<Tr, THREADS, ITEMS, MINB, LBB, (LBT >> 8)>;
     }
     // per-device one-time setup: opt in to the dynamic shared memory, read the occupancy
     static cudaError_t prepare(int* resident) {
@@ -110,7 +116,7 @@ struct PassLauncher {
             e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
             if (e != cudaSuccess) return e;
             int per_sm = 0, sms = 0;
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, THREADS + LBT, SMEM);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, BLOCK, SMEM);
             if (e != cudaSuccess) return e;
             e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
             if (e != cudaSuccess) return e;
@@ -127,7 +133,7 @@ struct PassLauncher {
         if (e != cudaSuccess) return e;
         unsigned grid = a.num_tiles;
         if (KERNEL >= 1 && grid > (unsigned)resident) grid = (unsigned)resident;
-        kernel()<<<grid, THREADS + LBT, SMEM, st>>>(a);
+        kernel()<<<grid, BLOCK, SMEM, st>>>(a);
         count_launch();
         return cudaGetLastError();
     }
@@ -201,6 +207,14 @@ struct SortCall {
     int hist_copy_words = 0;
     const void* splitters = nullptr;          // partition: nsplit raw keys (host)
     int nsplit = 0;
+    // partition, split in two calls around the caller's count exchange (fused multi-GPU path):
+    //   PHASE_COUNT   memset + K1 + K2: leaves histogram, plan and look-back state in ws
+    //   PHASE_SCATTER K3 only, on the state PHASE_COUNT left in the same ws; bucket r goes to
+    //                 peer_bases[r] (peer memory) starting at element peer_offsets[r]
+    enum { PHASE_ALL = 0, PHASE_COUNT = 1, PHASE_SCATTER = 2 };
+    int phase = PHASE_ALL;
+    void* const* peer_bases = nullptr;               // host array, nsplit + 1 device pointers
+    const unsigned long long* peer_offsets = nullptr;  // device array, nsplit + 1 element offsets
 };
 
 // entry points of the per-(family, width) front translation units

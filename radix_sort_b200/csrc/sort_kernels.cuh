@@ -62,6 +62,16 @@ __device__ __forceinline__ u128 ld_elem<u128>(const u128* p) {
     return r;
 }
 
+// Make a register value opaque to the optimiser.  Between the count and the
+// scatter the compiler otherwise keeps one precomputed counter address per key
+// alive across the digit scan (ITEMS extra registers at the point of highest
+// pressure); after this it recomputes them from the key (two ALU ops each).
+__device__ __forceinline__ void launder(unsigned char& v) { unsigned x = v; asm volatile("" : "+r"(x)); v = (unsigned char)x; }
+__device__ __forceinline__ void launder(unsigned short& v) { unsigned x = v; asm volatile("" : "+r"(x)); v = (unsigned short)x; }
+__device__ __forceinline__ void launder(unsigned int& v) { asm volatile("" : "+r"(v)); }
+__device__ __forceinline__ void launder(unsigned long long& v) { asm volatile("" : "+l"(v)); }
+__device__ __forceinline__ void launder(u128& v) { asm volatile("" : "+l"(v.lo), "+l"(v.hi)); }
+
 // ---------------------------------------------------------------------------
 // K1: all-digit histogram.  16-byte coalesced loads (LDG.128), four in flight
 // per thread; one privatised shared-memory histogram set per CTA, bumped with
@@ -379,11 +389,12 @@ __device__ __forceinline__ bool workers_sync_or(bool p) {
 // Decoupled look-back for one digit, LB_BATCH predecessors per round trip.
 // p points at the status word of tile `pos` (the nearest predecessor) for this
 // digit; tiles below 0 read as {INCLUSIVE, 0}.
+template <int B>
 struct LookBack {
-    uint32_t v[LB_BATCH];
+    uint32_t v[B];
     __device__ __forceinline__ void request(const uint32_t* p, int pos) {
 #pragma unroll
-        for (int j = 0; j < LB_BATCH; ++j)
+        for (int j = 0; j < B; ++j)
             v[j] = (pos - j >= 0) ? ld_relaxed_u32(p - (size_t)j * RADIX) : LB_FLAG_INCLUSIVE;
     }
     // sum of the counts of all preceding tiles
@@ -392,7 +403,7 @@ struct LookBack {
         for (;;) {
             bool done = false;
 #pragma unroll
-            for (int j = 0; j < LB_BATCH; ++j) {
+            for (int j = 0; j < B; ++j) {
                 if (!done) {
                     uint32_t x = v[j];
                     while ((x & (LB_FLAG_PARTIAL | LB_FLAG_INCLUSIVE)) == 0) x = ld_relaxed_u32(p - (size_t)j * RADIX);
@@ -401,8 +412,8 @@ struct LookBack {
                 }
             }
             if (done) return sum;
-            p -= (size_t)LB_BATCH * RADIX;
-            pos -= LB_BATCH;
+            p -= (size_t)B * RADIX;
+            pos -= B;
             request(p, pos);
         }
     }
@@ -414,6 +425,17 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
                                           uint32_t xf_out, uint32_t tile_n, int tid) {
     using E = typename Tr::elem_t;
     bool bad = false;
+    if constexpr (Tr::FEW_BUCKETS) {
+        // long runs, expensive digit: copy run by run, no digit per key
+        const int buckets = a.prm.nsplit + 1;
+        for (int b = 0; b < buckets; ++b) {
+            const uint32_t lo = sh.excl[b], hi = lo + sh.cnt[b];
+            const unsigned long long base = sh.gptr[b];
+            for (uint32_t idx = lo + tid; idx < hi; idx += THREADS)
+                *reinterpret_cast<E*>(base + (unsigned long long)idx * sizeof(E)) = sh.tile[idx];
+        }
+        return false;
+    }
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
         const uint32_t idx = (uint32_t)j * THREADS + tid;
@@ -433,13 +455,12 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
 // construction) from the keys still in global memory, and rewrite its slots.
 // Entered by a whole CTA; warp_hist may hold anything; excl/gptr are valid.
 template <typename Tr, int THREADS, int ITEMS, int LBT>
-__device__ __noinline__ void rerank_tile(const PassShared<Tr, THREADS, ITEMS>* shp,
+__device__ __noinline__ void rerank_tile(const PassShared<Tr, THREADS, ITEMS> sh,
                                          const PassArgs<Tr>* ap, const typename Tr::elem_t* src_tile,
                                          uint32_t tile_n, uint32_t xf_in, uint32_t xf_out) {
     using E = typename Tr::elem_t;
     constexpr int WARPS = THREADS / 32;
     const PassArgs<Tr>& a = *ap;
-    const PassShared<Tr, THREADS, ITEMS> sh = *shp;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lane_lt = (1u << lane) - 1u;
     const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
@@ -480,11 +501,12 @@ struct NoHook { __device__ __forceinline__ void operator()() const {} };
 // WORKERS threads rank the tile.  LBT == 0: the last 256 of them also run the
 // look-back, in line.  LBT > 0: LBT extra threads (the look-back warps of the
 // persistent kernel) run it concurrently and hand sh.gptr over at BAR_GPTR.
-template <typename Tr, int WORKERS, int ITEMS, bool FULL, int LBT, typename Hook>
+template <typename Tr, int WORKERS, int ITEMS, bool FULL, int LBT, int LBB, int ABL = 0, typename Hook = NoHook,
+          typename Hook2 = NoHook>
 __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, ITEMS>& sh, const PassArgs<Tr>& a,
                                                  const PassPlan& pp, typename Tr::elem_t (&e)[ITEMS],
                                                  typename Tr::elem_t* __restrict__ dst, uint32_t tile, uint32_t tile_n,
-                                                 Hook after_count) {
+                                                 Hook after_count = Hook{}, Hook2 after_scatter = Hook2{}) {
     using E = typename Tr::elem_t;
     constexpr int WARPS = WORKERS / 32;
     constexpr int LB0 = WORKERS - RADIX;  // in-line look-back: the last 256 threads
@@ -500,24 +522,64 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     // ---- 1. count: the warp's counters become its digit histogram
     uint32_t* my_hist = sh.warp_hist + warp * RADIX;
     uint32_t rank[Tr::NEEDS_STABLE ? ITEMS : 1];
+    unsigned code[Tr::FEW_BUCKETS ? (ITEMS + 7) / 8 : 1] = {};  // FEW_BUCKETS: 4-bit digit of every key
     if (Tr::NEEDS_STABLE) {
         const unsigned lane_lt = (1u << lane) - 1u;
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
             rank[Tr::NEEDS_STABLE ? i : 0] =
                 ballot_rank<FULL>(Tr::digit(e[i], pass, a.prm), FULL || wbase + i * 32 < tile_n, my_hist, lane, lane_lt);
+    } else if constexpr (Tr::FEW_BUCKETS) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+            if (FULL || wbase + i * 32 < tile_n) {
+                const unsigned d = Tr::digit(e[i], pass, a.prm);
+                code[i / 8] |= d << (4 * (i % 8));
+                atomicAdd(&my_hist[d], 1u);
+            }
     } else {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
             if (FULL || wbase + i * 32 < tile_n) atomicAdd(&my_hist[Tr::digit(e[i], pass, a.prm)], 1u);
     }
+    if constexpr (ABL & 64) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) launder(e[i]);
+    }
     workers_sync<WORKERS, LBT>();
     after_count();  // persistent kernel: thread 0 starts the bulk copy of the next tile
+
+    // ---- decoupled look-back in line, one digit per thread of the last 256 threads.
+    // EARLY: the first batch of predecessors is requested here and resolved right
+    // after the digit scan, BEFORE the scatter -- the tile's INCLUSIVE words then
+    // appear one scatter-time sooner, and every later tile's walk is that much shorter.
+    constexpr bool EARLY = (LBT == 0) && ((ABL & 32) != 0);
+    uint32_t* lb = a.lookback + (size_t)tile * RADIX;
+    LookBack<LBB> look;
+    if (EARLY && tid >= LB0 && tile > 0) look.request(lb - RADIX + (tid - LB0), (int)tile - 1);
+    auto lookback_inline = [&](bool requested) {
+        if (tid >= LB0) {
+            const int d = tid - LB0;
+            const uint32_t cnt_d = sh.cnt[d];
+            unsigned long long excl_tiles = 0;
+            if (ABL & 1) {  // timing ablation: no polling, a plausible distinct address
+                excl_tiles = min((unsigned long long)tile * (WORKERS * ITEMS / RADIX),
+                                 (unsigned long long)a.portion_n - cnt_d - min((unsigned long long)a.portion_n - cnt_d, a.bins_in[d]));
+            } else if (tile > 0) {
+                if (!requested) look.request(lb - RADIX + d, (int)tile - 1);
+                const uint32_t sum = look.resolve(lb - RADIX + d, (int)tile - 1);
+                st_relaxed_u32(lb + d, LB_FLAG_INCLUSIVE | (sum + cnt_d));
+                excl_tiles = sum;
+            }
+            const unsigned long long gbase = a.bins_in[d] + excl_tiles;
+            sh.gptr[d] = Tr::dst_base((unsigned)d, dst, a.prm) + (gbase - sh.excl[d]) * sizeof(E);
+            if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[d] = gbase + cnt_d;
+        }
+    };
 
     // ---- 2. thread d owns digit d: tile count -> publish -> scan over digits ->
     // per-warp first slots inside the digit-sorted tile
     uint32_t count = 0;
-    uint32_t* lb = a.lookback + (size_t)tile * RADIX;
     if (tid < RADIX) {
         count = column_total<WARPS>(sh.warp_hist, tid);
         st_relaxed_u32(lb + tid, (tile == 0 ? LB_FLAG_INCLUSIVE : LB_FLAG_PARTIAL) | count);
@@ -542,40 +604,29 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     }
     if constexpr (LBT > 0) bar_arrive<BAR_EXCL, WORKERS + LBT>();
     workers_sync<WORKERS, LBT>();
+    if constexpr (EARLY) lookback_inline(true);
 
     // ---- 3. scatter: the returned counter value IS the key's slot in the tile
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i)
         if (FULL || wbase + i * 32 < tile_n) {
-            const unsigned d = Tr::digit(e[i], pass, a.prm);
-            const uint32_t slot = Tr::NEEDS_STABLE ? rank[Tr::NEEDS_STABLE ? i : 0] + my_hist[d] : atomicAdd(&my_hist[d], 1u);
+            const unsigned d = Tr::FEW_BUCKETS ? (code[Tr::FEW_BUCKETS ? i / 8 : 0] >> (4 * (i % 8))) & 15u : Tr::digit(e[i], pass, a.prm);
+            const uint32_t slot = (ABL & 8) ? wbase + i * 32 + (d & 0u)
+                                  : Tr::NEEDS_STABLE ? rank[Tr::NEEDS_STABLE ? i : 0] + my_hist[d] : atomicAdd(&my_hist[d], 1u);
             sh.tile[slot] = e[i];
         }
+    after_scatter();  // e[] is dead from here on: the streaming kernel re-fills it with the next tile
 
     if constexpr (LBT == 0) {
-        // ---- decoupled look-back in line, one digit per thread of the last 256 threads
-        if (tid >= LB0) {
-            const int d = tid - LB0;
-            const uint32_t cnt_d = sh.cnt[d];
-            unsigned long long excl_tiles = 0;
-            if (tile > 0) {
-                LookBack look;
-                look.request(lb - RADIX + d, (int)tile - 1);
-                const uint32_t sum = look.resolve(lb - RADIX + d, (int)tile - 1);
-                st_relaxed_u32(lb + d, LB_FLAG_INCLUSIVE | (sum + cnt_d));
-                excl_tiles = sum;
-            }
-            const unsigned long long gbase = a.bins_in[d] + excl_tiles;
-            sh.gptr[d] = (unsigned long long)dst + (gbase - sh.excl[d]) * sizeof(E);
-            if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[d] = gbase + cnt_d;
-        }
+        if constexpr (!EARLY) lookback_inline(false);
         __syncthreads();
     } else {
         bar_sync<BAR_GPTR, WORKERS + LBT>();  // scatter done by all workers + sh.gptr published
     }
 
     // ---- coalesced run write-out; key-only passes check the order of the tile
-    if (Tr::NEEDS_STABLE || pass == 0) {
+    if (ABL & 4) return false;
+    if (Tr::NEEDS_STABLE || pass == 0 || (ABL & 2)) {
         write_out<Tr, WORKERS, ITEMS, FULL, false>(sh, a, pp.xf_out, tile_n, tid);
         return false;
     }
@@ -648,13 +699,13 @@ __device__ __forceinline__ void lookback_role(const PassShared<Tr, WORKERS, ITEM
     for (int q = 0; q < NDL; ++q) {
         const int d = q * LBT + ltid;
         const unsigned long long gbase = bin[q] + sum[q];
-        sh.gptr[d] = (unsigned long long)dst + (gbase - sh.excl[d]) * sizeof(E);
+        sh.gptr[d] = Tr::dst_base((unsigned)d, dst, a.prm) + (gbase - sh.excl[d]) * sizeof(E);
         if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[d] = gbase + sh.cnt[d];
     }
     bar_arrive<BAR_GPTR, WORKERS + LBT>();
 }
 
-template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS>
+template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS, int LBB = LB_BATCH, int ABL = 0>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     using E = typename Tr::elem_t;
@@ -694,17 +745,17 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     if (tile_n == (uint32_t)TILE) {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) e[i] = ld_elem(src_tile + wbase + i * 32);
-        bad = rank_and_scatter<Tr, THREADS, ITEMS, true, 0>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
+        bad = rank_and_scatter<Tr, THREADS, ITEMS, true, 0, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
     } else {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
             if (wbase + i * 32 < tile_n) e[i] = ld_elem(src_tile + wbase + i * 32);
-        bad = rank_and_scatter<Tr, THREADS, ITEMS, false, 0>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
+        bad = rank_and_scatter<Tr, THREADS, ITEMS, false, 0, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
     }
-    if (Tr::NEEDS_STABLE || a.pass == 0) return;
+    if (Tr::NEEDS_STABLE || a.pass == 0 || (ABL & 31) != 0) return;
     if (!__syncthreads_or(bad)) return;
     if (tid == 0) atomicAdd(a.stats, 1u);
-    rerank_tile<Tr, THREADS, ITEMS, 0>(&sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
+    rerank_tile<Tr, THREADS, ITEMS, 0>(sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
 }
 
 // ---- TMA bulk copy + mbarrier (sm_90+ PTX; SASS: UBLKCP / SYNCS) ------------------
@@ -812,13 +863,13 @@ onesweep_persistent_kernel(const __grid_constant__ PassArgs<Tr> a) {
             mbar_wait(&sh.mbar[slot], (it >> 1) & 1u);
 #pragma unroll
             for (int i = 0; i < ITEMS; ++i) e[i] = sh.tile[wbase + i * 32];
-            bad = rank_and_scatter<Tr, WORKERS, ITEMS, true, LBT>(sh, a, pp, e, dst, tile, tile_n, prefetch);
+            bad = rank_and_scatter<Tr, WORKERS, ITEMS, true, LBT, LB_BATCH>(sh, a, pp, e, dst, tile, tile_n, prefetch);
         } else {  // the ragged last tile of the portion: plain guarded loads
             tile_n = a.portion_n - tile * (uint32_t)TILE;
 #pragma unroll
             for (int i = 0; i < ITEMS; ++i)
                 if (wbase + i * 32 < tile_n) e[i] = ld_elem(src_tile + wbase + i * 32);
-            bad = rank_and_scatter<Tr, WORKERS, ITEMS, false, LBT>(sh, a, pp, e, dst, tile, tile_n, prefetch);
+            bad = rank_and_scatter<Tr, WORKERS, ITEMS, false, LBT, LB_BATCH>(sh, a, pp, e, dst, tile, tile_n, prefetch);
         }
         // counters are free once the scatter is over (BAR_GPTR inside rank_and_scatter)
 #pragma unroll
@@ -826,7 +877,7 @@ onesweep_persistent_kernel(const __grid_constant__ PassArgs<Tr> a) {
         fence_proxy_async();  // generic-proxy accesses of this slot before the next bulk copy into it
         if (workers_sync_or<WORKERS, LBT>(bad)) {
             if (tid == 0) atomicAdd(a.stats, 1u);
-            rerank_tile<Tr, WORKERS, ITEMS, LBT>(&sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
+            rerank_tile<Tr, WORKERS, ITEMS, LBT>(sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
             for (int i = tid; i < WARPS * RADIX; i += WORKERS) sh.warp_hist[i] = 0;
             fence_proxy_async();
             workers_sync<WORKERS, LBT>();

@@ -21,6 +21,16 @@ Equal keys are bit-identical for key-only sorts, so which GPU holds which copy
 of a duplicated key is unobservable; a splitter value that is heavily
 duplicated simply lands whole on one rank (load imbalance, not an error).
 
+Fused form (`sort_sharded(..., exchange=PeerExchange(...))`): steps 3-5 become
+    3'. b200sort_partition_count_device   one read: per-destination counts
+    4'. all_gather(counts) -> for every destination, the offset in ITS receive
+        buffer at which this rank's keys start
+    5'. b200sort_partition_exchange_device  K7 storing every bucket straight into
+        the destination GPU's receive buffer (peer memory over NVLink, mapped by
+        torch symmetric memory) + one device-side barrier
+so the keys cross NVLink inside the partition kernel's write-out and are never
+staged in a send buffer or copied by a separate collective.
+
 The device steps go through an `ops` object so that the host-side logic (sample
 positions, splitter choice, count exchange, offsets) runs under gloo on CPU in
 tests/ with a numpy test double; the default ops are the CUDA C ABI and fail
@@ -64,6 +74,45 @@ def exchange_plan(count_matrix: np.ndarray, rank: int):
     recv_counts) of `rank` as python int lists."""
     cm = np.asarray(count_matrix, dtype=np.int64)
     return [int(x) for x in cm[rank, :]], [int(x) for x in cm[:, rank]]
+
+
+def send_offsets(count_matrix: np.ndarray, rank: int):
+    """Element offset, in every destination's receive buffer, at which the keys
+    sent by `rank` start: receive buffers are filled in sender-rank order, so it
+    is the number of keys lower ranks send to that destination."""
+    cm = np.asarray(count_matrix, dtype=np.int64)
+    return [int(x) for x in cm[:rank, :].sum(axis=0)]
+
+
+class PeerExchange:
+    """Receive buffers of all ranks of `group`, each `capacity_keys` keys, mapped
+    into every process (torch symmetric memory: CUDA VMM allocations exchanged
+    between the processes, P2P over NVLink / NVSwitch).  Collective constructor;
+    reuse one instance across sorts -- the rendezvous is the expensive part.
+
+    Re-use protocol: a rank's peers start storing into its receive buffer after
+    the count all_gather of the NEXT sort, which that rank enqueues on the same
+    stream after whatever consumed the previous result; consume the result on
+    the stream sort_sharded ran on (or synchronise with it) before the next call."""
+
+    def __init__(self, capacity_keys: int, key_bytes: int, device, group=None):
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        if not torch.cuda.is_available():
+            raise B200SortError(3, "peer exchange needs CUDA devices (there is no CPU fallback)")
+        self.capacity = int(capacity_keys)
+        self.key_bytes = int(key_bytes)
+        self.group = group if group is not None else dist.group.WORLD
+        self.buf = symm.empty(self.capacity * self.key_bytes, dtype=torch.uint8, device=device)
+        self.handle = symm.rendezvous(self.buf, self.group)
+        self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.recv_rows = self.buf.view(self.capacity, self.key_bytes)
+
+    def barrier(self):
+        """Device-side barrier on the current stream: every rank's stores into
+        every receive buffer are complete and visible after it."""
+        self.handle.barrier(channel=0)
 
 
 class CudaOps:
@@ -116,8 +165,47 @@ class CudaOps:
         workspace.record_stream(self.torch.cuda.current_stream(self.device))
         return counts
 
+    def partition_count(self, rows, kind: Kind, splitters_host: np.ndarray, workspace):
+        """K7 count phase; leaves its state in `workspace` for partition_exchange."""
+        n = rows.shape[0]
+        nsplit = int(splitters_host.shape[0])
+        counts = self.torch.zeros(nsplit + 1, dtype=self.torch.int64, device=self.device)
+        spl = np.ascontiguousarray(splitters_host)
+        check(self.lib.b200sort_partition_count_device(rows.data_ptr(), workspace.data_ptr(), workspace.numel(), n, int(kind),
+                                                       spl.ctypes.data if nsplit else None, nsplit, counts.data_ptr(),
+                                                       self._stream()))
+        return counts
+
+    def partition_exchange(self, rows, kind: Kind, splitters_host: np.ndarray, workspace, exchange, offsets):
+        """K7 scatter phase storing into the peers' receive buffers; `offsets`: device
+        int64 tensor, element offset of this rank's keys in every destination."""
+        n = rows.shape[0]
+        nsplit = int(splitters_host.shape[0])
+        spl = np.ascontiguousarray(splitters_host)
+        bases = (ctypes.c_void_p * (nsplit + 1))(*exchange.peer_ptrs[: nsplit + 1])
+        check(self.lib.b200sort_partition_exchange_device(rows.data_ptr(), workspace.data_ptr(), workspace.numel(), n,
+                                                          int(kind), spl.ctypes.data if nsplit else None, nsplit, bases,
+                                                          offsets.data_ptr(), self._stream()))
+        workspace.record_stream(self.torch.cuda.current_stream(self.device))
+        exchange.barrier()
+
+    def workspace_for(self, n: int, kind: Kind, workspace=None):
+        need = temp_bytes(max(n, 1), kind)
+        if workspace is None or workspace.numel() < need:
+            workspace = self.torch.empty(need, dtype=self.torch.uint8, device=self.device)
+        return workspace
+
     def to_host(self, t) -> np.ndarray:
         return t.cpu().numpy()
+
+    def mark(self):
+        ev = self.torch.cuda.Event(enable_timing=True)
+        ev.record(self.torch.cuda.current_stream(self.device))
+        return ev
+
+    def elapsed_ms(self, a, b) -> float:
+        b.synchronize()
+        return float(a.elapsed_time(b))
 
 
 @dataclass
@@ -130,11 +218,17 @@ class ShardedResult:
 
 
 def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 << 14, seed: int = 0xB200,
-                 workspace=None, send_buffer=None) -> ShardedResult:
+                 workspace=None, send_buffer=None, exchange=None, timings: Optional[dict] = None) -> ShardedResult:
     """Sort keys sharded over the ranks of `group`.  `keys`: this rank's shard
     (contiguous CUDA tensor; (n, 2) uint64 for 128-bit kinds).  Collective: every
     rank of the group must call it.  Returns this rank's slice of the sorted order
-    (same dtype as `keys`)."""
+    (same dtype as `keys`).
+
+    exchange: a PeerExchange -> fused path (K7 stores into the peers' receive
+    buffers; the result is a view of this rank's receive buffer).  A sort whose
+    largest shard would not fit the exchange's capacity falls back, on all ranks
+    together, to the all-to-all path.  timings: dict filled with per-phase
+    milliseconds (device time on the current stream)."""
     import torch
     import torch.distributed as dist
     k = Kind(kind)
@@ -153,6 +247,18 @@ def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 
     def typed(r):
         return r.reshape(-1).view(keys.dtype).reshape((-1,) + tail)
 
+    marks = []
+
+    def mark(name):
+        if timings is not None and hasattr(ops, "mark"):
+            marks.append((name, ops.mark()))
+
+    def finish():
+        if timings is not None and marks:
+            for (_, a), (name, b) in zip(marks[:-1], marks[1:]):
+                timings[name] = timings.get(name, 0.0) + ops.elapsed_ms(a, b)
+
+    mark("start")
     if world == 1:
         ops.local_sort(rows, k, workspace)
         return ShardedResult(keys, n_local, [n_local], [n_local], np.zeros((0, kb), dtype=np.uint8))
@@ -175,6 +281,28 @@ def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 
     if len(picks) != world - 1:  # no keys anywhere
         return ShardedResult(keys[:0], 0, [0] * world, [0] * world, np.zeros((0, kb), dtype=np.uint8))
     splitters = np.ascontiguousarray(np.stack(picks))
+    mark("splitters")
+
+    if exchange is not None:
+        # 3'. count  4'. count matrix -> where my keys start in every receive buffer
+        ws = ops.workspace_for(n_local, k, workspace)
+        counts = ops.partition_count(rows, k, splitters, ws)
+        rws = [torch.zeros_like(counts) for _ in range(world)]
+        dist.all_gather(rws, counts, group=group)
+        cm = np.stack([ops.to_host(r) for r in rws])
+        send_counts, recv_counts = exchange_plan(cm, rank)
+        n_out = sum(recv_counts)
+        mark("count")
+        if int(cm.sum(axis=0).max()) <= exchange.capacity:  # same decision on every rank
+            offsets = torch.tensor(send_offsets(cm, rank), dtype=torch.int64).to(rows.device)
+            # 5'. K7 scatter into the peers' receive buffers + barrier
+            ops.partition_exchange(rows, k, splitters, ws, exchange, offsets)
+            mark("exchange")
+            recv = exchange.recv_rows[:n_out]
+            ops.local_sort(recv, k, ws)
+            mark("local_sort")
+            finish()
+            return ShardedResult(typed(recv), n_out, send_counts, recv_counts, splitters)
 
     # 3. K7: partition by destination rank
     if send_buffer is None or send_buffer.numel() * send_buffer.element_size() < n_local * kb:
@@ -182,6 +310,7 @@ def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 
     else:
         send = send_buffer.view(torch.uint8).reshape(-1)[: n_local * kb].reshape(n_local, kb)
     counts = ops.partition(rows, send, k, splitters, workspace)
+    mark("partition")
 
     # 4. count matrix
     rws = [torch.zeros_like(counts) for _ in range(world)]
@@ -193,7 +322,10 @@ def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 
     # 5. all-to-all: split sizes count rows (= keys)
     recv = ops.empty_rows(n_out, kb)
     dist.all_to_all_single(recv, send, output_split_sizes=recv_counts, input_split_sizes=send_counts, group=group)
+    mark("all_to_all")
 
     # 6. local LSD sort of the received range
     ops.local_sort(recv, k, workspace)
+    mark("local_sort")
+    finish()
     return ShardedResult(typed(recv), n_out, send_counts, recv_counts, splitters)

@@ -49,6 +49,42 @@ class NumpyOps:
     def to_host(self, t):
         return t.numpy()
 
+    # ---- fused path: count, then "peer stores" emulated over gloo.  Every sender
+    # ships (offset it computed, bucket) pairs; the receiver writes each bucket at
+    # the SENDER's offset, so wrong offsets from mgpu.send_offsets corrupt the result.
+    def workspace_for(self, n, kind, workspace=None):
+        return None
+
+    def _dest(self, rows, splitters_host):
+        a = self._u64(rows)
+        spl = splitters_host.reshape(-1).view(np.uint64)
+        return a, np.searchsorted(spl, a, side="right")
+
+    def partition_count(self, rows, kind, splitters_host, workspace):
+        a, dest = self._dest(rows, splitters_host)
+        return torch.from_numpy(np.bincount(dest, minlength=len(splitters_host) + 1).astype(np.int64))
+
+    def partition_exchange(self, rows, kind, splitters_host, workspace, exchange, offsets):
+        a, dest = self._dest(rows, splitters_host)
+        world = dist.get_world_size()
+        mine = [(int(offsets[d]), a[dest == d].copy()) for d in range(world)]
+        everyone = [None] * world
+        dist.all_gather_object(everyone, mine)
+        recv = exchange.recv_rows.numpy().reshape(-1).view(np.uint64)
+        me = dist.get_rank()
+        for sender in range(world):
+            off, part = everyone[sender][me]
+            assert off + len(part) <= exchange.capacity
+            recv[off: off + len(part)] = part
+
+
+class FakeExchange:
+    """Stands in for mgpu.PeerExchange: a local receive buffer of `capacity` keys."""
+
+    def __init__(self, capacity, key_bytes=8):
+        self.capacity = capacity
+        self.recv_rows = torch.full((capacity, key_bytes), 0xEE, dtype=torch.uint8)
+
 
 def _free_port():
     s = socket.socket()
@@ -58,7 +94,7 @@ def _free_port():
     return port
 
 
-def _worker(rank, world, port, n_per_rank, mode, q):
+def _worker(rank, world, port, n_per_rank, mode, q, fused=False, capacity=0):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -72,20 +108,26 @@ def _worker(rank, world, port, n_per_rank, mode, q):
             a = rng.integers(0, 2**63, size=n_per_rank if rank == 0 else 0, dtype=np.int64)
         keys = torch.from_numpy(a.copy())
         # int64 tensor holding u64 bit patterns < 2^63 (same order either way)
-        res = mgpu.sort_sharded(keys, Kind.U64, ops=NumpyOps(), samples_per_rank=512)
+        exchange = FakeExchange(capacity) if fused else None
+        res = mgpu.sort_sharded(keys, Kind.U64, ops=NumpyOps(), samples_per_rank=512, exchange=exchange)
+        if fused and capacity >= 2 * n_per_rank:  # the result must be a view of the receive buffer
+            assert res.keys.data_ptr() == exchange.recv_rows.data_ptr()
         out = res.keys.numpy().copy()
         q.put((rank, a, out, res.send_counts, res.recv_counts))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mode", ["uniform", "few_unique", "ragged"])
-def test_sort_sharded_world2_gloo(mode):
+@pytest.mark.parametrize("mode,fused,capacity", [("uniform", False, 0), ("few_unique", False, 0), ("ragged", False, 0),
+                                                 ("uniform", True, 40_000), ("few_unique", True, 40_000),
+                                                 ("ragged", True, 40_000),
+                                                 ("uniform", True, 100)])  # too small: all ranks fall back together
+def test_sort_sharded_world2_gloo(mode, fused, capacity):
     world, n = 2, 20_000
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, n, mode, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, mode, q, fused, capacity)) for r in range(world)]
     [p.start() for p in procs]
     got = {}
     for _ in range(world):
@@ -115,6 +157,11 @@ def test_sample_positions_and_splitters_are_deterministic():
     assert mgpu.choose_splitters(s[:0], 4) == []
     send, recv = mgpu.exchange_plan(np.array([[1, 2], [3, 4]]), rank=0)
     assert send == [1, 2] and recv == [1, 3]
+    # receive buffers fill in sender order: rank 1's keys start after rank 0's
+    cm = np.array([[1, 2, 3], [4, 5, 6], [7, 8, 9]])
+    assert mgpu.send_offsets(cm, 0) == [0, 0, 0]
+    assert mgpu.send_offsets(cm, 1) == [1, 2, 3]
+    assert mgpu.send_offsets(cm, 2) == [5, 7, 9]
 
 
 def test_cuda_ops_refuse_to_run_without_a_gpu():

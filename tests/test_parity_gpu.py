@@ -352,6 +352,57 @@ def test_partition_by_splitters(kind, cuda):
     assert _ref.same_bits(d_in.cpu().numpy(), a)  # input untouched
 
 
+@pytest.mark.parametrize("kind", ["u32", "u64", "f64"])
+def test_partition_count_then_exchange_into_separate_buffers(kind, cuda):
+    """The fused multi-GPU form of K7 on one device: every destination has its own
+    receive buffer ("peer" pointer) and this rank's keys start at a given offset in
+    each, as if lower ranks had already claimed the space before it."""
+    import torch
+    n = 1_200_003
+    a = _ref.random_keys(kind, n, seed=57)
+    srt = _ref.expected_sorted(a, kind)
+    nsplit = 3
+    spl = np.ascontiguousarray(srt[[n * (j + 1) // (nsplit + 1) for j in range(nsplit)]])
+    if kind in ("f32", "f64"):
+        keyv = _ref.total_cmp_key(a.view(np.int32 if kind == "f32" else np.int64))
+        splv = _ref.total_cmp_key(spl.view(np.int32 if kind == "f32" else np.int64))
+    else:
+        keyv, splv = a, spl
+    dest = np.searchsorted(splv, keyv, side="right")
+    want_counts = np.bincount(dest, minlength=nsplit + 1)
+
+    L = _ffi.lib()
+    k = _kind(kind)
+    d_in = _to_device(a, cuda)
+    ws = torch.empty(rs.temp_bytes(n, k), dtype=torch.uint8, device=cuda)
+    counts = torch.zeros(nsplit + 1, dtype=torch.int64, device=cuda)
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    rc = L.b200sort_partition_count_device(d_in.data_ptr(), ws.data_ptr(), ws.numel(), n, int(k), spl.ctypes.data, nsplit,
+                                           counts.data_ptr(), st)
+    assert rc == 0, L.b200sort_last_error()
+    assert counts.cpu().numpy().tolist() == want_counts.tolist()
+
+    offs = [5, 0, 1234, 77]  # where "my" keys start in each destination's buffer
+    fill = 0xEE
+    bufs = [torch.full(((offs[r] + int(want_counts[r]) + 9) * a.itemsize,), fill, dtype=torch.uint8, device=cuda)
+            .view(d_in.dtype) for r in range(nsplit + 1)]
+    bases = (ctypes.c_void_p * (nsplit + 1))(*[b.data_ptr() for b in bufs])
+    d_offs = torch.tensor(offs, dtype=torch.int64, device=cuda)
+    rc = L.b200sort_partition_exchange_device(d_in.data_ptr(), ws.data_ptr(), ws.numel(), n, int(k), spl.ctypes.data, nsplit,
+                                              bases, d_offs.data_ptr(), st)
+    assert rc == 0, L.b200sort_last_error()
+    torch.cuda.synchronize()
+    pad = np.frombuffer(bytes([fill]) * a.itemsize, dtype=a.dtype)[0]
+    for r in range(nsplit + 1):
+        got = bufs[r].cpu().numpy()
+        c = int(want_counts[r])
+        assert _ref.same_bits(got[offs[r]: offs[r] + c], a[dest == r]), f"destination {r}"
+        # nothing outside [offset, offset + count) was touched
+        assert _ref.same_bits(got[: offs[r]], np.full(offs[r], pad, dtype=a.dtype))
+        assert _ref.same_bits(got[offs[r] + c:], np.full(9, pad, dtype=a.dtype))
+    assert _ref.same_bits(d_in.cpu().numpy(), a)
+
+
 # ---- full-size runs: size-independent properties (sorted + same multiset) ------------
 
 def _property_run(kind, n, dist, param, cuda, seed=0xB2000002):
