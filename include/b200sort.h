@@ -90,6 +90,14 @@ int b200sort_keys_device_ex(void *d_keys, void *d_tmp, size_t tmp_bytes, size_t 
  * copies back into `keys`, blocks until done.  Owns its device memory. */
 int b200sort_keys_host(void *keys, size_t n, int kind);
 
+/* Host slices of at least this many bytes (default 64 MiB) take the pipelined
+ * form of b200sort_keys_host: the keys are split into 16 key ranges on the
+ * device (K7, splitters sampled from the host slice), the ranges are sorted one
+ * after the other and each is copied back while the next is being sorted.  Same
+ * result, the device->host copy overlaps the sort.  0 = always, SIZE_MAX = never
+ * (tests use both). */
+int b200sort_set_host_pipeline_min_bytes(size_t bytes);
+
 /* Key-value records, key = field 0 of a `(K, V)` tuple (radix_digits.rs:126-136;
  * call sites tests.rs:182, main.rs:112,123).  Stable.  rec_bytes is the whole
  * record (8 for (u32,u32), 16 for (u64,u64)); the key of `kind` sits at byte

@@ -202,6 +202,12 @@ def set_variant(key_bytes_: int, variant: int) -> None:
     check(_ffi.lib().b200sort_set_variant(key_bytes_, variant))
 
 
+def set_host_pipeline_min_bytes(nbytes: int) -> None:
+    """Host slices of at least `nbytes` take the pipelined host path (range split
+    + copy-out overlapped with the range sorts); 0 = always, 2**64-1 = never."""
+    check(_ffi.lib().b200sort_set_host_pipeline_min_bytes(int(nbytes)))
+
+
 def num_variants(key_bytes_: int) -> int:
     return int(_ffi.lib().b200sort_num_variants(key_bytes_))
 

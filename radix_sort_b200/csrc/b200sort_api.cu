@@ -8,7 +8,9 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -187,6 +189,128 @@ int host_roundtrip(void* host, size_t bytes, size_t ws_bytes, SortFn sort) {
     return B200SORT_OK;
 }
 
+
+// ---- pipelined host path (keys, large inputs) ---------------------------------------
+// The plain round trip serialises copy-in, sort and copy-out: 8 GB + 8 GB over
+// PCIe around a 39 ms sort.  The copy-in cannot overlap the sort (every pass
+// needs all keys), but the copy-out can: split the keys into 16 key ranges
+// first (one K7 pass with splitters sampled from the host buffer), sort the
+// ranges one after the other, and start the device->host copy of a range as
+// soon as it is sorted, on a second stream.  The ranges are contiguous and in
+// order in the partition output, so the host buffer ends up exactly as the plain
+// path leaves it.
+std::atomic<size_t> g_pipeline_min_bytes{(size_t)64 << 20};
+constexpr int PIPE_GROUPS = MAX_SPLITTERS + 1;
+
+template <typename U>
+void host_splitters(const void* host, size_t n, int xf, U* out_raw) {
+    const unsigned char* base = static_cast<const unsigned char*>(host);
+    const size_t S = std::min<size_t>(n, (size_t)1 << 14);
+    const size_t stride = n / S;
+    std::vector<U> s(S);
+    for (size_t i = 0; i < S; ++i) {
+        U raw;
+        std::memcpy(&raw, base + (i * stride + (size_t)(mix64(i) % stride)) * sizeof(U), sizeof(U));
+        s[i] = to_ordered_rt<U>(raw, xf);
+    }
+    std::sort(s.begin(), s.end(), [](const U& a, const U& b) { return ordered_less<U>(a, b); });
+    for (int j = 0; j < MAX_SPLITTERS; ++j) out_raw[j] = from_ordered_rt<U>(s[S * (size_t)(j + 1) / PIPE_GROUPS], xf);
+}
+
+struct Trace {  // B200SORT_TRACE=1: wall-clock marks of the host path on stderr
+    bool on = std::getenv("B200SORT_TRACE") != nullptr;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    void mark(const char* what) {
+        if (!on) return;
+        const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        std::fprintf(stderr, "[b200sort] %8.2f ms  %s\n", ms, what);
+    }
+};
+
+int keys_host_pipelined(void* host, size_t n, int kind) {
+    Trace tr;
+    const size_t kb = b200sort_key_bytes(kind);
+    const size_t bytes = n * kb;
+    const size_t data = align_up(bytes, 256);
+    const size_t ws_part = align_up(temp_by_width<FAM_PARTITION>(kb, n), 256);
+    const size_t counts_bytes = 256;
+    void* block = nullptr;
+    int rc = pool_acquire(2 * data + ws_part + counts_bytes, &block);
+    if (rc) return rc;
+    struct Cleanup {
+        void* block; void* extra = nullptr; cudaStream_t s = nullptr, c = nullptr; cudaEvent_t ev[PIPE_GROUPS] = {};
+        ~Cleanup() {
+            if (s) cudaStreamSynchronize(s);
+            if (c) cudaStreamSynchronize(c);
+            for (auto e : ev) if (e) cudaEventDestroy(e);
+            if (s) cudaStreamDestroy(s);
+            if (c) cudaStreamDestroy(c);
+            if (extra) pool_release(extra);
+            pool_release(block);
+        }
+    } cl{block};
+    CU(cudaStreamCreateWithFlags(&cl.s, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&cl.c, cudaStreamNonBlocking));
+    unsigned char* d_in = static_cast<unsigned char*>(block);
+    unsigned char* d_out = d_in + data;
+    unsigned char* d_ws = d_out + data;
+    uint64_t* d_counts = reinterpret_cast<uint64_t*>(d_ws + ws_part);
+
+    tr.mark("streams + device block ready");
+    CU(cudaMemcpyAsync(d_in, host, bytes, cudaMemcpyHostToDevice, cl.s));
+    tr.mark("copy-in enqueued");
+    // splitters from the host copy, while the DMA runs
+    alignas(16) unsigned char spl[MAX_SPLITTERS * 16];
+    const int xf = kind_xf(kind);
+    switch (kb) {
+    case 1: host_splitters<unsigned char>(host, n, xf, reinterpret_cast<unsigned char*>(spl)); break;
+    case 2: host_splitters<unsigned short>(host, n, xf, reinterpret_cast<unsigned short*>(spl)); break;
+    case 4: host_splitters<unsigned int>(host, n, xf, reinterpret_cast<unsigned int*>(spl)); break;
+    case 8: host_splitters<unsigned long long>(host, n, xf, reinterpret_cast<unsigned long long*>(spl)); break;
+    default: host_splitters<u128>(host, n, xf, reinterpret_cast<u128*>(spl)); break;
+    }
+    tr.mark("splitters chosen");
+    if (tr.on) { cudaStreamSynchronize(cl.s); tr.mark("copy-in done"); }
+    rc = b200sort_partition_device(d_in, d_out, d_ws, ws_part, n, kind, spl, MAX_SPLITTERS, d_counts, cl.s);
+    if (rc) return rc;
+    uint64_t counts[PIPE_GROUPS];
+    CU(cudaMemcpyAsync(counts, d_counts, sizeof(counts), cudaMemcpyDeviceToHost, cl.s));
+    CU(cudaStreamSynchronize(cl.s));
+    tr.mark("range split done, counts on the host");
+
+    // the input buffer is free now: it is the workspace of the range sorts
+    size_t max_g = 0;
+    for (int g = 0; g < PIPE_GROUPS; ++g) max_g = std::max<size_t>(max_g, (size_t)counts[g]);
+    unsigned char* ws_sort = d_in;
+    size_t ws_sort_bytes = data;
+    const size_t need = b200sort_temp_bytes(max_g, kind);
+    if (need > ws_sort_bytes) {  // heavily skewed keys: one range holds most of them
+        rc = pool_acquire(need, &cl.extra);
+        if (rc) return rc;
+        ws_sort = static_cast<unsigned char*>(cl.extra);
+        ws_sort_bytes = need;
+    }
+    size_t off = 0;
+    for (int g = 0; g < PIPE_GROUPS; ++g) {
+        const size_t cnt = (size_t)counts[g];
+        if (cnt == 0) continue;
+        rc = keys_device_dispatch(d_out + off * kb, ws_sort, ws_sort_bytes, cnt, kind, cl.s, 0, nullptr, 0);
+        if (rc) return rc;
+        CU(cudaEventCreateWithFlags(&cl.ev[g], cudaEventDisableTiming));
+        CU(cudaEventRecord(cl.ev[g], cl.s));
+        CU(cudaStreamWaitEvent(cl.c, cl.ev[g], 0));
+        CU(cudaMemcpyAsync(static_cast<unsigned char*>(host) + off * kb, d_out + off * kb, cnt * kb, cudaMemcpyDeviceToHost, cl.c));
+        off += cnt;
+    }
+    if (off != n) return fail(B200SORT_ERR_CUDA, "partition counts do not add up to n");
+    tr.mark("range sorts + copy-outs enqueued");
+    CU(cudaStreamSynchronize(cl.s));
+    tr.mark("range sorts done");
+    CU(cudaStreamSynchronize(cl.c));
+    tr.mark("copy-out done");
+    return B200SORT_OK;
+}
+
 }  // namespace
 
 // ---- exported C ABI ------------------------------------------------------------------
@@ -233,10 +357,16 @@ int b200sort_keys_host(void* keys, size_t n, int kind) {
     if (kb == 0) return fail(B200SORT_ERR_UNSUPPORTED_KIND, "unknown key kind " + std::to_string(kind));
     if (n == 0) return B200SORT_OK;
     if (!keys) return fail(B200SORT_ERR_INVALID_ARG, "null host pointer");
+    if (n * kb >= g_pipeline_min_bytes.load(std::memory_order_relaxed) && n >= 4096) return keys_host_pipelined(keys, n, kind);
     const size_t ws = b200sort_temp_bytes(n, kind);
     return host_roundtrip(keys, n * kb, ws, [&](void* d, void* w, size_t wb, cudaStream_t st) {
         return keys_device_dispatch(d, w, wb, n, kind, st, 0, nullptr, 0);
     });
+}
+
+int b200sort_set_host_pipeline_min_bytes(size_t bytes) {
+    g_pipeline_min_bytes.store(bytes, std::memory_order_relaxed);
+    return B200SORT_OK;
 }
 
 size_t b200sort_records_temp_bytes(size_t n, size_t rec_bytes, int kind) {

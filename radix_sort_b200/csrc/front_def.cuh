@@ -25,7 +25,7 @@ size_t temp_bytes_front(size_t n) {
     size_t m = 0;
     for (int i = 0; i < num_variants<FAM, W>(); ++i) {
         const VariantDesc d = Variants<FAM, W>::v[i];
-        const size_t t = make_layout(n ? n : 1, W, Tr::DIGITS, d.threads * d.items).total;
+        const size_t t = make_layout(n ? n : 1, W, Tr::DIGITS, d.threads * d.items, FAM != FAM_PARTITION).total;
         if (t > m) m = t;
     }
     return m;
@@ -88,12 +88,13 @@ int sort_front(const SortCall& c) {
     if ((Variants<FAM, W>::v[variant].kernel == 1 || Variants<FAM, W>::v[variant].kernel == 2) && !aligned16) variant = Variants<FAM, W>::FALLBACK;
     const VariantDesc vd = Variants<FAM, W>::v[variant];
     const int tile = vd.threads * vd.items;
-    const Layout L = make_layout(n, W, D, tile);
+    const Layout L = make_layout(n, W, D, tile, FAM != FAM_PARTITION);
     if (c.ws_bytes < L.total) return fail(B200SORT_ERR_INVALID_ARG, "workspace smaller than b200sort_temp_bytes()");
 
     unsigned char* ws = static_cast<unsigned char*>(c.ws);
     // alt_out: single-pass callers (the multi-GPU partition) name the destination
     // themselves; the result stays there and nothing is copied back
+    if (FAM == FAM_PARTITION && !c.alt_out) return fail(B200SORT_ERR_INVALID_ARG, "partition needs a destination");
     E* tmp = c.alt_out ? static_cast<E*>(c.alt_out) : reinterpret_cast<E*>(ws + L.tmp_off);
     unsigned long long* bins = reinterpret_cast<unsigned long long*>(ws + L.bins_off);
     Plan* plan = reinterpret_cast<Plan*>(ws + L.plan_off);

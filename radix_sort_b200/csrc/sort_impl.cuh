@@ -141,6 +141,7 @@ struct PassLauncher {
 
 // ---- workspace layout -----------------------------------------------------------
 // [ tmp elements | bins D*P*256 u64 | plan | hist D*256 u64 | tickets D*P u32 | stats | look-back ]
+// (the partition family always writes to a caller-named destination: no tmp region)
 //                                          ^--------- zeroed by one memset ---------------^
 struct Layout {
     size_t tmp_off, bins_off, plan_off, hist_off, ticket_off, stats_off, lb_off, total;
@@ -150,7 +151,7 @@ struct Layout {
     size_t tiles_total;    // tiles over all portions (one pass)
 };
 
-inline Layout make_layout(size_t n, size_t elem_bytes, int digits, int tile) {
+inline Layout make_layout(size_t n, size_t elem_bytes, int digits, int tile, bool with_tmp = true) {
     Layout L{};
     const size_t max_portion = ((size_t)LB_VALUE_MASK / tile) * tile;  // < 2^30, whole tiles
     L.portion_elems = max_portion;
@@ -162,7 +163,7 @@ inline Layout make_layout(size_t n, size_t elem_bytes, int digits, int tile) {
         L.tiles_total += (pn + tile - 1) / tile;
     }
     size_t off = 0;
-    L.tmp_off = off;    off = align_up(off + n * elem_bytes, 256);
+    L.tmp_off = off;    off = align_up(off + (with_tmp ? n * elem_bytes : 0), 256);
     L.bins_off = off;   off = align_up(off + (size_t)digits * L.portions * RADIX * 8, 256);
     L.plan_off = off;   off = align_up(off + sizeof(Plan), 256);
     L.hist_off = off;   off = align_up(off + (size_t)digits * RADIX * 8, 256);

@@ -592,12 +592,14 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
         const uint32_t y = __shfl_up_sync(FULL_MASK, incl, o);
         if (lane >= o) incl += y;
     }
-    if (lane == 31 && warp < RADIX / 32) sh.misc[2 + warp] = incl;
+    // (bits 16+: how many of this warp's 32 digits occur in the tile at all)
+    const unsigned occupied = __ballot_sync(FULL_MASK, count != 0);
+    if (lane == 31 && warp < RADIX / 32) sh.misc[2 + warp] = incl | ((uint32_t)__popc(occupied) << 16);
     workers_sync<WORKERS, LBT>();
     if (tid < RADIX) {
         uint32_t base = 0;
 #pragma unroll
-        for (int w = 0; w < RADIX / 32; ++w) base += (w < warp) ? sh.misc[2 + w] : 0u;
+        for (int w = 0; w < RADIX / 32; ++w) base += (w < warp) ? (sh.misc[2 + w] & 0xFFFFu) : 0u;
         const uint32_t excl = base + incl - count;  // keys of the tile with a smaller digit
         sh.excl[tid] = excl;
         column_bases<WARPS>(sh.warp_hist, tid, excl);
@@ -606,7 +608,35 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     workers_sync<WORKERS, LBT>();
     if constexpr (EARLY) lookback_inline(true);
 
-    // ---- 3. scatter: the returned counter value IS the key's slot in the tile
+    // ---- 3. scatter: the returned counter value IS the key's slot in the tile.
+    // A returning shared atomic serialises lanes that hit the SAME counter (25 cycles
+    // per warp instruction when all 32 do, 14 when two counters share them --
+    // profiles/r01_microbench_atomics_skew.txt).  Two cheap ways out:
+    //   * one digit in the whole tile (sorted input, clustered keys): the tile is
+    //     already in order, slot = position;
+    //   * the partition kernel (2..16 buckets, registers to spare): match_any groups
+    //     the lanes, one atomic per group -- ~10 cycles, lane-ordered by construction.
+    uint32_t distinct = 0;
+    if constexpr (FULL && !Tr::NEEDS_STABLE && (ABL & 8) == 0) {
+#pragma unroll
+        for (int w = 0; w < RADIX / 32; ++w) distinct += sh.misc[2 + w] >> 16;
+    }
+    if (FULL && !Tr::NEEDS_STABLE && distinct == 1) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) sh.tile[wbase + i * 32] = e[i];
+    } else if (Tr::FEW_BUCKETS && FULL && distinct <= 3) {
+        const unsigned lane_lt = (1u << lane) - 1u;
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const unsigned d = (code[Tr::FEW_BUCKETS ? i / 8 : 0] >> (4 * (i % 8))) & 15u;
+            const unsigned m = __match_any_sync(FULL_MASK, d);
+            const int leader = __ffs(m) - 1;
+            uint32_t base = 0;
+            if (lane == leader) base = atomicAdd(&my_hist[d], (uint32_t)__popc(m));
+            base = __shfl_sync(FULL_MASK, base, leader);
+            sh.tile[base + __popc(m & lane_lt)] = e[i];
+        }
+    } else
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i)
         if (FULL || wbase + i * 32 < tile_n) {

@@ -103,6 +103,29 @@ def test_host_path_small_and_odd(kind, cuda):
         _check_host(_ref.random_keys(kind, n, seed=n + 7), kind)
 
 
+@pytest.mark.parametrize("kind", _ref.KINDS)
+def test_host_path_pipelined(kind, cuda):
+    """The large-slice form of b200sort_keys_host (16 key ranges, copy-out overlapped
+    with the range sorts), forced at small sizes: same bits as the plain path."""
+    rs.set_host_pipeline_min_bytes(0)
+    try:
+        for n in (4096, 100_003, 1_000_001):
+            _check_host(_ref.random_keys(kind, n, seed=n + 11), kind)
+        # skewed inputs: empty ranges, one range holding everything, repeated splitters
+        n = 200_000
+        base = _ref.random_keys(kind, n, seed=5)
+        allsame = base.copy(); allsame[:] = base[0]
+        few = base.copy(); few[:] = base[np.arange(n) % 3]
+        mostly = base.copy(); mostly[: n - 100] = base[0]
+        presorted = _ref.expected_sorted(base, kind)
+        for a in (allsame, few, mostly, presorted, np.ascontiguousarray(presorted[::-1])):
+            _check_host(a, kind)
+        if kind in ("f32", "f64"):
+            _check_host(_ref.float_test_keys(kind, 150_000, seed=3), kind)
+    finally:
+        rs.set_host_pipeline_min_bytes(64 << 20)
+
+
 @pytest.mark.parametrize("kind", ["u8", "u16", "u32", "u64", "i32", "i64", "f32", "f64", "u128"])
 def test_degenerate_inputs_skip_and_no_skip(kind, cuda):
     import torch

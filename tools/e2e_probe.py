@@ -1,0 +1,46 @@
+"""Where does the end-to-end time of b200sort_keys_host go?  Raw pinned H2D / D2H
+rates next to the plain and the pipelined host path.  Dev tool."""
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+import radix_sort_b200 as rs
+from radix_sort_b200 import _ffi, distr
+
+n = int(float(sys.argv[1])) if len(sys.argv) > 1 else 1_000_000_000
+dev = torch.device("cuda:0")
+K = rs.Kind.U64
+src = distr.empty_keys(n, K, dev)
+distr.generate(src, K, distr.Distr.UNIFORM, 0, seed=1)
+host = torch.empty(n, dtype=torch.uint64, pin_memory=True)
+d = torch.empty_like(src)
+
+
+def timed(fn, reps=3):
+    best = 1e9
+    for _ in range(reps):
+        torch.cuda.synchronize()
+        t = time.perf_counter()
+        fn()
+        torch.cuda.synchronize()
+        best = min(best, time.perf_counter() - t)
+    return best * 1e3
+
+
+host.copy_(src)
+print("H2D 8n bytes  ms", round(timed(lambda: d.copy_(host, non_blocking=True)), 2))
+print("D2H 8n bytes  ms", round(timed(lambda: host.copy_(d, non_blocking=True)), 2))
+L = _ffi.lib()
+for name, thr in (("plain", 2**63), ("pipelined", 0)):
+    rs.set_host_pipeline_min_bytes(thr)
+    best = 1e9
+    for _ in range(3):
+        host.copy_(src)
+        torch.cuda.synchronize()
+        t = time.perf_counter()
+        _ffi.check(L.b200sort_keys_host(host.data_ptr(), n, int(K)))
+        best = min(best, time.perf_counter() - t)
+    print(name, "keys_host ms", round(best * 1e3, 2), "Gkeys/s", round(n / best / 1e9, 3))
