@@ -263,7 +263,7 @@ onesweep_ring_kernel(const __grid_constant__ PassArgs<Tr> a) {
         } else {
 #pragma unroll
             for (int i = 0; i < ITEMS; ++i)
-                if (full || wbase + i * 32 < tile_n) atomicAdd(&my_hist[Tr::digit(e[i], pass, a.prm)], 1u);
+                if (full || wbase + i * 32 < tile_n) atomicAdd(&my_hist[hidx(Tr::digit(e[i], pass, a.prm))], 1u);
         }
         bar_sync<BAR_WORKERS, WORKERS>();
         // the slot two tiles back was written out during the last iteration: refill it
@@ -302,7 +302,7 @@ onesweep_ring_kernel(const __grid_constant__ PassArgs<Tr> a) {
         for (int i = 0; i < ITEMS; ++i)
             if (full || wbase + i * 32 < tile_n) {
                 const unsigned d = Tr::digit(e[i], pass, a.prm);
-                const uint32_t s = Tr::NEEDS_STABLE ? rank[Tr::NEEDS_STABLE ? i : 0] + my_hist[d] : atomicAdd(&my_hist[d], 1u);
+                const uint32_t s = Tr::NEEDS_STABLE ? rank[Tr::NEEDS_STABLE ? i : 0] + my_hist[hidx(d)] : atomicAdd(&my_hist[hidx(d)], 1u);
                 cur[s] = e[i];
             }
 

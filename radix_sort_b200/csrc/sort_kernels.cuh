@@ -309,6 +309,13 @@ struct PassShared {
     }
 };
 
+// Counter of digit d inside a 256-counter histogram.  Counter index = bank, so
+// digits that are multiples of 16 or 32 (stride-2^k sequences, floats made from
+// small integers) would pile onto one or two banks; folding the top three bits
+// into the low five spreads them (a bijection; r01 sweep v14: ascending u32,
+// pass 0, 1.54 -> 1.04 ms).
+__device__ __forceinline__ unsigned hidx(unsigned d) { return d ^ (d >> 5); }
+
 // lane-ordered rank of one item inside its warp: 8 ballots -> lanes with my digit
 template <bool FULL_TILE>
 __device__ __forceinline__ uint32_t ballot_rank(unsigned d, bool valid, uint32_t* my_hist, int lane, unsigned lane_lt) {
@@ -321,7 +328,7 @@ __device__ __forceinline__ uint32_t ballot_rank(unsigned d, bool valid, uint32_t
     }
     const int leader = __ffs(m) - 1;
     uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(&my_hist[d], (uint32_t)__popc(m));
+    if (lane == leader) base = atomicAdd(&my_hist[hidx(d)], (uint32_t)__popc(m));
     base = __shfl_sync(FULL_MASK, base, leader & 31);
     return base + __popc(m & lane_lt);
 }
@@ -331,7 +338,7 @@ template <int WARPS>
 __device__ __forceinline__ uint32_t column_total(const uint32_t* warp_hist, int d) {
     uint32_t c = 0;
 #pragma unroll
-    for (int w = 0; w < WARPS; ++w) c += warp_hist[w * RADIX + d];
+    for (int w = 0; w < WARPS; ++w) c += warp_hist[w * RADIX + hidx(d)];
     return c;
 }
 template <int WARPS>
@@ -339,8 +346,8 @@ __device__ __forceinline__ void column_bases(uint32_t* warp_hist, int d, uint32_
     uint32_t run = start;
 #pragma unroll
     for (int w = 0; w < WARPS; ++w) {
-        const uint32_t t = warp_hist[w * RADIX + d];
-        warp_hist[w * RADIX + d] = run;
+        const uint32_t t = warp_hist[w * RADIX + hidx(d)];
+        warp_hist[w * RADIX + hidx(d)] = run;
         run += t;
     }
 }
@@ -484,7 +491,7 @@ __device__ __noinline__ void rerank_tile(const PassShared<Tr, THREADS, ITEMS> sh
     workers_sync<THREADS, LBT>();
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i)
-        if (wbase + i * 32 < tile_n) sh.tile[rank[i] + my_hist[Tr::digit(e[i], a.pass, a.prm)]] = e[i];
+        if (wbase + i * 32 < tile_n) sh.tile[rank[i] + my_hist[hidx(Tr::digit(e[i], a.pass, a.prm))]] = e[i];
     workers_sync<THREADS, LBT>();
     write_out<Tr, THREADS, ITEMS, false, false>(sh, a, xf_out, tile_n, tid);
     workers_sync<THREADS, LBT>();
@@ -535,12 +542,12 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
             if (FULL || wbase + i * 32 < tile_n) {
                 const unsigned d = Tr::digit(e[i], pass, a.prm);
                 code[i / 8] |= d << (4 * (i % 8));
-                atomicAdd(&my_hist[d], 1u);
+                atomicAdd(&my_hist[hidx(d)], 1u);
             }
     } else {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
-            if (FULL || wbase + i * 32 < tile_n) atomicAdd(&my_hist[Tr::digit(e[i], pass, a.prm)], 1u);
+            if (FULL || wbase + i * 32 < tile_n) atomicAdd(&my_hist[hidx(Tr::digit(e[i], pass, a.prm))], 1u);
     }
     if constexpr (ABL & 64) {
 #pragma unroll
@@ -632,7 +639,7 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
             const unsigned m = __match_any_sync(FULL_MASK, d);
             const int leader = __ffs(m) - 1;
             uint32_t base = 0;
-            if (lane == leader) base = atomicAdd(&my_hist[d], (uint32_t)__popc(m));
+            if (lane == leader) base = atomicAdd(&my_hist[hidx(d)], (uint32_t)__popc(m));
             base = __shfl_sync(FULL_MASK, base, leader);
             sh.tile[base + __popc(m & lane_lt)] = e[i];
         }
@@ -642,7 +649,7 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
         if (FULL || wbase + i * 32 < tile_n) {
             const unsigned d = Tr::FEW_BUCKETS ? (code[Tr::FEW_BUCKETS ? i / 8 : 0] >> (4 * (i % 8))) & 15u : Tr::digit(e[i], pass, a.prm);
             const uint32_t slot = (ABL & 8) ? wbase + i * 32 + (d & 0u)
-                                  : Tr::NEEDS_STABLE ? rank[Tr::NEEDS_STABLE ? i : 0] + my_hist[d] : atomicAdd(&my_hist[d], 1u);
+                                  : Tr::NEEDS_STABLE ? rank[Tr::NEEDS_STABLE ? i : 0] + my_hist[hidx(d)] : atomicAdd(&my_hist[hidx(d)], 1u);
             sh.tile[slot] = e[i];
         }
     after_scatter();  // e[] is dead from here on: the streaming kernel re-fills it with the next tile
