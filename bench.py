@@ -314,12 +314,41 @@ def run_gpu(args):
     except Exception:  # noqa: BLE001
         pass
 
+    # ---- the metric names u32 too: the same workload shape with 4-byte keys (N = 1 only), reported beside the headline
+    u32_line = None
+    if world == 1 and not args.no_u32:
+        K4 = rs.Kind.U32
+        p4 = distr.empty_keys(n, K4, dev)
+        distr.generate(p4, K4, distr.Distr.UNIFORM, 0, seed=SEED)
+        k4 = torch.empty_like(p4)
+        fp4 = verify.fingerprint(p4, K4)
+        t4 = 0.0
+        for i in range(2 + args.steps):
+            k4.copy_(p4)
+            torch.cuda.synchronize()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            rs.radix_sort(k4, K4, workspace=ws)
+            a1.record()
+            torch.cuda.synchronize()
+            if i >= 2:
+                t4 += a0.elapsed_time(a1)
+        if verify.count_unsorted(k4, K4) != 0 or verify.fingerprint(k4, K4) != fp4:
+            raise SystemExit("u32 sort failed verification")
+        k4.copy_(p4)
+        tt4 = rs.sort_timed(k4, K4, workspace=ws, flags=rs.FLAG_NO_SKIP)
+        ap4 = sum(tt4["pass_ms"]) / len(tt4["pass_ms"])
+        u32_line = {"value": round(n / (t4 / args.steps * 1e-3) / 1e9, 3), "unit": "Gkeys/s", "ms_per_step": round(t4 / args.steps, 4),
+                    "workload": f"uniform random u32 keys, {n} elements, single B200", "pass_GBps": round(2.0 * n * 4 / (ap4 * 1e-3) / 1e9, 1),
+                    "pass_frac": round(2.0 * n * 4 / (ap4 * 1e-3) / 1e9 / peak, 4)}
+        del p4, k4
+
     # ---- e2e: host buffers through the drop-in C-ABI call, copies inside the timed region
-    e2e_steps = max(1, min(args.steps, 5))
-    host = torch.empty(n if world == 1 else int(n * 1.25) + 1024, dtype=torch.uint64, pin_memory=True)
+    e2e_steps = 0 if args.no_e2e else max(1, min(args.steps, 5))
+    host = torch.empty(1 if args.no_e2e else n if world == 1 else int(n * 1.25) + 1024, dtype=torch.uint64, pin_memory=True)
     e2e_total = 0.0
     h2d = d2h = n * KEY_BYTES
-    for i in range(e2e_steps + 1):
+    for i in range(e2e_steps + 1 if e2e_steps else 0):
         host[:n].copy_(pristine)  # untimed: a fresh unsorted HOST input
         barrier()
         t0 = time.perf_counter()
@@ -338,8 +367,8 @@ def run_gpu(args):
     te = torch.tensor([e2e_total], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = world * n / (float(te.item()) / e2e_steps) / 1e9
-    if world == 1:
+    e2e_value = world * n / (float(te.item()) / e2e_steps) / 1e9 if e2e_steps else None
+    if world == 1 and e2e_steps:
         hs = host[:n]
         assert bool((hs[1:].view(torch.int64) ^ (-2**63) >= hs[:-1].view(torch.int64) ^ (-2**63)).all()), "e2e result not sorted"
 
@@ -368,7 +397,7 @@ def run_gpu(args):
                    "keys_per_gpu": n, "seed": SEED, "digits": DIGITS, "digit_bits": 8,
                    "l2": "inputs (8 GB/GPU) exceed the 126 MB L2; no flush between steps",
                    "e2e_steps": e2e_steps, "verified": "sorted + multiset fingerprint == input (bit-identical to the reference's output)"},
-        "e2e": {"value": round(e2e_value, 3), "unit": "Gkeys/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "e2e": {"value": round(e2e_value, 3) if e2e_value is not None else None, "unit": "Gkeys/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "onesweep pass (K3), one 8-bit digit", "achieved": round(achieved, 1), "peak": peak,
@@ -377,6 +406,8 @@ def run_gpu(args):
                      "hist_kernel_GBps": round(rf_n * KEY_BYTES / (sum(hist_ms) / len(hist_ms) * 1e-3) / 1e9, 1),
                      "whole_sort_GBps": round(KEY_BYTES * (1 + 2 * DIGITS) * world * n / (ms_per_step * 1e-3) / 1e9 / world, 1)},
     }
+    if u32_line is not None:
+        line["u32"] = u32_line
     if cpu is not None:
         line["cpu_baseline"] = cpu
     print(json.dumps(line), flush=True)
@@ -394,6 +425,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--keys", dest="n", type=int, default=N_KEYS, help="keys per GPU (default: the BASELINE.json workload)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-u32", action="store_true", help="skip the secondary u32 measurement")
+    ap.add_argument("--no-e2e", action="store_true",
+                    help="skip the host-buffer leg (evidence runs at sizes whose pinned host copies would not fit the box)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "fused", "nccl"],
                     help="N > 1: fused K7 peer stores, NCCL all-to-all, or fused with fallback (default)")
     args = ap.parse_args()

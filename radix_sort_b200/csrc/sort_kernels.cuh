@@ -62,16 +62,6 @@ __device__ __forceinline__ u128 ld_elem<u128>(const u128* p) {
     return r;
 }
 
-// Make a register value opaque to the optimiser.  Between the count and the
-// scatter the compiler otherwise keeps one precomputed counter address per key
-// alive across the digit scan (ITEMS extra registers at the point of highest
-// pressure); after this it recomputes them from the key (two ALU ops each).
-__device__ __forceinline__ void launder(unsigned char& v) { unsigned x = v; asm volatile("" : "+r"(x)); v = (unsigned char)x; }
-__device__ __forceinline__ void launder(unsigned short& v) { unsigned x = v; asm volatile("" : "+r"(x)); v = (unsigned short)x; }
-__device__ __forceinline__ void launder(unsigned int& v) { asm volatile("" : "+r"(v)); }
-__device__ __forceinline__ void launder(unsigned long long& v) { asm volatile("" : "+l"(v)); }
-__device__ __forceinline__ void launder(u128& v) { asm volatile("" : "+l"(v.lo), "+l"(v.hi)); }
-
 // ---------------------------------------------------------------------------
 // K1: all-digit histogram.  16-byte coalesced loads (LDG.128), four in flight
 // per thread; one privatised shared-memory histogram set per CTA, bumped with
@@ -549,22 +539,16 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
         for (int i = 0; i < ITEMS; ++i)
             if (FULL || wbase + i * 32 < tile_n) atomicAdd(&my_hist[hidx(Tr::digit(e[i], pass, a.prm))], 1u);
     }
-    if constexpr (ABL & 64) {
-#pragma unroll
-        for (int i = 0; i < ITEMS; ++i) launder(e[i]);
-    }
     workers_sync<WORKERS, LBT>();
     after_count();  // persistent kernel: thread 0 starts the bulk copy of the next tile
 
-    // ---- decoupled look-back in line, one digit per thread of the last 256 threads.
-    // EARLY: the first batch of predecessors is requested here and resolved right
-    // after the digit scan, BEFORE the scatter -- the tile's INCLUSIVE words then
-    // appear one scatter-time sooner, and every later tile's walk is that much shorter.
-    constexpr bool EARLY = (LBT == 0) && ((ABL & 32) != 0);
+    // ---- decoupled look-back in line, one digit per thread of the last 256 threads,
+    // run AFTER the scatter.  (Requesting the first batch here and resolving it
+    // before the scatter publishes INCLUSIVE words sooner, but the walk then meets
+    // predecessors that have not even published their counts and spins: 5-30 %
+    // slower, profiles/r01_sweep_v12_early_lookback.jsonl.)
     uint32_t* lb = a.lookback + (size_t)tile * RADIX;
-    LookBack<LBB> look;
-    if (EARLY && tid >= LB0 && tile > 0) look.request(lb - RADIX + (tid - LB0), (int)tile - 1);
-    auto lookback_inline = [&](bool requested) {
+    auto lookback_inline = [&]() {
         if (tid >= LB0) {
             const int d = tid - LB0;
             const uint32_t cnt_d = sh.cnt[d];
@@ -573,7 +557,8 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
                 excl_tiles = min((unsigned long long)tile * (WORKERS * ITEMS / RADIX),
                                  (unsigned long long)a.portion_n - cnt_d - min((unsigned long long)a.portion_n - cnt_d, a.bins_in[d]));
             } else if (tile > 0) {
-                if (!requested) look.request(lb - RADIX + d, (int)tile - 1);
+                LookBack<LBB> look;
+                look.request(lb - RADIX + d, (int)tile - 1);
                 const uint32_t sum = look.resolve(lb - RADIX + d, (int)tile - 1);
                 st_relaxed_u32(lb + d, LB_FLAG_INCLUSIVE | (sum + cnt_d));
                 excl_tiles = sum;
@@ -613,7 +598,6 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     }
     if constexpr (LBT > 0) bar_arrive<BAR_EXCL, WORKERS + LBT>();
     workers_sync<WORKERS, LBT>();
-    if constexpr (EARLY) lookback_inline(true);
 
     // ---- 3. scatter: the returned counter value IS the key's slot in the tile.
     // A returning shared atomic serialises lanes that hit the SAME counter (25 cycles
@@ -655,7 +639,7 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     after_scatter();  // e[] is dead from here on: the streaming kernel re-fills it with the next tile
 
     if constexpr (LBT == 0) {
-        if constexpr (!EARLY) lookback_inline(false);
+        lookback_inline();
         __syncthreads();
     } else {
         bar_sync<BAR_GPTR, WORKERS + LBT>();  // scatter done by all workers + sh.gptr published
