@@ -63,7 +63,7 @@ template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{
 #define B200_NV_KEYS_2 3
 template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}, {3, 512, 24, 2, 0}, {1, 448, 24, 2, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_4 5
-template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{3, 512, 22, 2, 0}, {0, 512, 22, 2, 0}, {0, 512, 16, 2, 0}, {1, 384, 20, 2, 128}, {2, 384, 16, 2, 128}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 22, 2, 0}, {3, 512, 22, 2, 0}, {0, 512, 16, 2, 0}, {1, 384, 20, 2, 128}, {2, 384, 16, 2, 128}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_8 5
 template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {3, 512, 16, 2, 0}, {0, 512, 12, 2, 0}, {1, 384, 12, 2, 128}, {2, 384, 10, 2, 128}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_16 3

@@ -576,6 +576,10 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
         count = column_total<WARPS>(sh.warp_hist, tid);
         st_relaxed_u32(lb + tid, (tile == 0 ? LB_FLAG_INCLUSIVE : LB_FLAG_PARTIAL) | count);
         sh.cnt[tid] = count;
+        // a digit that holds more than half of the tile (at most one can) is ranked
+        // without atomics in the scatter; the word is tagged with the tile id so a
+        // stale one is never mistaken for this tile's
+        if (count * 2 > tile_n) sh.misc[10] = ((tile + 1u) << 8) | (uint32_t)tid;
     }
     if constexpr (LBT > 0) bar_arrive<BAR_CNT, WORKERS + LBT>();  // the look-back warps start now
     uint32_t incl = count;
@@ -601,41 +605,65 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
 
     // ---- 3. scatter: the returned counter value IS the key's slot in the tile.
     // A returning shared atomic serialises lanes that hit the SAME counter (25 cycles
-    // per warp instruction when all 32 do, 14 when two counters share them --
-    // profiles/r01_microbench_atomics_skew.txt).  Two cheap ways out:
-    //   * one digit in the whole tile (sorted input, clustered keys): the tile is
-    //     already in order, slot = position;
-    //   * the partition kernel (2..16 buckets, registers to spare): match_any groups
-    //     the lanes, one atomic per group -- ~10 cycles, lane-ordered by construction.
-    uint32_t distinct = 0;
-    if constexpr (FULL && !Tr::NEEDS_STABLE && (ABL & 8) == 0) {
+    // per warp instruction when all 32 do, 14 when two counters share them, 4 from
+    // 16 counters up -- profiles/r01_microbench_atomics_skew.txt), which is what
+    // clustered, sorted, few-unique or heavy-headed inputs produce.  So the keys of
+    // the tile's dominant digit (if one holds more than half of the tile) take no
+    // atomic at all: one ballot gives their lane-ordered rank inside the instruction,
+    // a running count in a register the rest -- lane-ordered by construction.  The
+    // other keys are few and take the atomic.  The partition kernel (2..16 buckets,
+    // registers to spare) groups lanes with match_any when a tile has <= 3 buckets.
+    if constexpr (Tr::FEW_BUCKETS) {
+        uint32_t distinct = 0;
+        if constexpr (FULL) {
 #pragma unroll
-        for (int w = 0; w < RADIX / 32; ++w) distinct += sh.misc[2 + w] >> 16;
-    }
-    if (FULL && !Tr::NEEDS_STABLE && distinct == 1) {
+            for (int w = 0; w < RADIX / 32; ++w) distinct += sh.misc[2 + w] >> 16;
+        }
+        if (FULL && distinct <= 3) {
+            const unsigned lane_lt = (1u << lane) - 1u;
 #pragma unroll
-        for (int i = 0; i < ITEMS; ++i) sh.tile[wbase + i * 32] = e[i];
-    } else if (Tr::FEW_BUCKETS && FULL && distinct <= 3) {
+            for (int i = 0; i < ITEMS; ++i) {
+                const unsigned d = (code[Tr::FEW_BUCKETS ? i / 8 : 0] >> (4 * (i % 8))) & 15u;
+                const unsigned m = __match_any_sync(FULL_MASK, d);
+                const int leader = __ffs(m) - 1;
+                uint32_t base = 0;
+                if (lane == leader) base = atomicAdd(&my_hist[hidx(d)], (uint32_t)__popc(m));
+                base = __shfl_sync(FULL_MASK, base, leader);
+                sh.tile[base + __popc(m & lane_lt)] = e[i];
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i)
+                if (FULL || wbase + i * 32 < tile_n) {
+                    const unsigned d = (code[Tr::FEW_BUCKETS ? i / 8 : 0] >> (4 * (i % 8))) & 15u;
+                    sh.tile[atomicAdd(&my_hist[hidx(d)], 1u)] = e[i];
+                }
+        }
+    } else if constexpr (Tr::NEEDS_STABLE || (ABL & 8) != 0) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+            if (FULL || wbase + i * 32 < tile_n) {
+                const unsigned d = Tr::digit(e[i], pass, a.prm);
+                const uint32_t slot = (ABL & 8) ? wbase + i * 32 + (d & 0u) : rank[Tr::NEEDS_STABLE ? i : 0] + my_hist[hidx(d)];
+                sh.tile[slot] = e[i];
+            }
+    } else {
+        const uint32_t domw = sh.misc[10];
+        const unsigned dom = (domw >> 8) == ((tile + 1u) & 0xFFFFFFu) ? (domw & 0xFFu) : 0x100u;  // 0x100: no dominant digit
+        uint32_t dom_slot = my_hist[hidx(dom & 0xFFu)];  // next free slot of the dominant digit in this warp's range
         const unsigned lane_lt = (1u << lane) - 1u;
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
-            const unsigned d = (code[Tr::FEW_BUCKETS ? i / 8 : 0] >> (4 * (i % 8))) & 15u;
-            const unsigned m = __match_any_sync(FULL_MASK, d);
-            const int leader = __ffs(m) - 1;
-            uint32_t base = 0;
-            if (lane == leader) base = atomicAdd(&my_hist[hidx(d)], (uint32_t)__popc(m));
-            base = __shfl_sync(FULL_MASK, base, leader);
-            sh.tile[base + __popc(m & lane_lt)] = e[i];
+            const bool valid = FULL || wbase + i * 32 < tile_n;
+            const unsigned d = Tr::digit(e[i], pass, a.prm);
+            const bool is_dom = valid && d == dom;
+            const unsigned m = __ballot_sync(FULL_MASK, is_dom);
+            uint32_t slot = dom_slot + (uint32_t)__popc(m & lane_lt);
+            dom_slot += (uint32_t)__popc(m);
+            if (valid && !is_dom) slot = atomicAdd(&my_hist[hidx(d)], 1u);
+            if (valid) sh.tile[slot] = e[i];
         }
-    } else
-#pragma unroll
-    for (int i = 0; i < ITEMS; ++i)
-        if (FULL || wbase + i * 32 < tile_n) {
-            const unsigned d = Tr::FEW_BUCKETS ? (code[Tr::FEW_BUCKETS ? i / 8 : 0] >> (4 * (i % 8))) & 15u : Tr::digit(e[i], pass, a.prm);
-            const uint32_t slot = (ABL & 8) ? wbase + i * 32 + (d & 0u)
-                                  : Tr::NEEDS_STABLE ? rank[Tr::NEEDS_STABLE ? i : 0] + my_hist[hidx(d)] : atomicAdd(&my_hist[hidx(d)], 1u);
-            sh.tile[slot] = e[i];
-        }
+    }
     after_scatter();  // e[] is dead from here on: the streaming kernel re-fills it with the next tile
 
     if constexpr (LBT == 0) {
