@@ -577,9 +577,10 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
         st_relaxed_u32(lb + tid, (tile == 0 ? LB_FLAG_INCLUSIVE : LB_FLAG_PARTIAL) | count);
         sh.cnt[tid] = count;
         // a digit that holds more than half of the tile (at most one can) is ranked
-        // without atomics in the scatter; the word is tagged with the tile id so a
-        // stale one is never mistaken for this tile's
-        if (count * 2 > tile_n) sh.misc[10] = ((tile + 1u) << 8) | (uint32_t)tid;
+        // without atomics in the scatter; the word is tagged with tile id and pass so
+        // that a stale one (shared memory survives launches) is not taken for this
+        // tile's -- and if it ever were, any digit is a correct choice, only slower
+        if (count * 2 > tile_n) sh.misc[10] = ((tile + 1u) << 12) | ((uint32_t)(pass & 15) << 8) | (uint32_t)tid;
     }
     if constexpr (LBT > 0) bar_arrive<BAR_CNT, WORKERS + LBT>();  // the look-back warps start now
     uint32_t incl = count;
@@ -649,8 +650,12 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
             }
     } else {
         const uint32_t domw = sh.misc[10];
-        const unsigned dom = (domw >> 8) == ((tile + 1u) & 0xFFFFFFu) ? (domw & 0xFFu) : 0x100u;  // 0x100: no dominant digit
-        uint32_t dom_slot = my_hist[hidx(dom & 0xFFu)];  // next free slot of the dominant digit in this warp's range
+        // no digit above half of the tile: the digit of the warp's first key stands in
+        // (any choice is correct; on sorted input, whose tiles straddle two runs, it
+        // is the warp's own dominant digit)
+        const unsigned dom = (domw >> 8) == ((((tile + 1u) << 4) | (uint32_t)(pass & 15)) & 0xFFFFFFu) ? (domw & 0xFFu)
+                                                                      : __shfl_sync(FULL_MASK, Tr::digit(e[0], pass, a.prm), 0);
+        uint32_t dom_slot = my_hist[hidx(dom)];  // next free slot of that digit in this warp's range
         const unsigned lane_lt = (1u << lane) - 1u;
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
