@@ -257,9 +257,23 @@ int keys_host_pipelined(void* host, size_t n, int kind) {
     uint64_t* d_counts = reinterpret_cast<uint64_t*>(d_ws + ws_part);
 
     tr.mark("streams + device block ready");
-    CU(cudaMemcpyAsync(d_in, host, bytes, cudaMemcpyHostToDevice, cl.s));
+    // the copy-in goes in chunks on the copy stream; while the DMA runs the host picks
+    // the splitters (1-2 ms), then every chunk is histogrammed by destination range on
+    // the compute stream as soon as it has landed: when the last byte arrives only
+    // the scatter of the range split is left to do
+    constexpr int CHUNKS = 16;
+    const size_t per_chunk = ((n + CHUNKS - 1) / CHUNKS + 4095) / 4096 * 4096;  // whole 16-byte vectors for K1
+    cudaEvent_t landed[CHUNKS] = {};
+    struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < CHUNKS; ++i) if (e[i]) cudaEventDestroy(e[i]); } } eg{landed};
+    for (int c = 0; c < CHUNKS; ++c) {
+        const size_t off = (size_t)c * per_chunk;
+        if (off >= n) break;
+        const size_t cnt = std::min(per_chunk, n - off);
+        CU(cudaMemcpyAsync(d_in + off * kb, static_cast<const unsigned char*>(host) + off * kb, cnt * kb, cudaMemcpyHostToDevice, cl.c));
+        CU(cudaEventCreateWithFlags(&landed[c], cudaEventDisableTiming));
+        CU(cudaEventRecord(landed[c], cl.c));
+    }
     tr.mark("copy-in enqueued");
-    // splitters from the host copy, while the DMA runs
     alignas(16) unsigned char spl[MAX_SPLITTERS * 16];
     const int xf = kind_xf(kind);
     switch (kb) {
@@ -270,9 +284,25 @@ int keys_host_pipelined(void* host, size_t n, int kind) {
     default: host_splitters<u128>(host, n, xf, reinterpret_cast<u128*>(spl)); break;
     }
     tr.mark("splitters chosen");
-    if (tr.on) { cudaStreamSynchronize(cl.s); tr.mark("copy-in done"); }
-    rc = b200sort_partition_device(d_in, d_out, d_ws, ws_part, n, kind, spl, MAX_SPLITTERS, d_counts, cl.s);
-    if (rc) return rc;
+    SortCall pc;
+    pc.elems = d_in; pc.alt_out = d_out; pc.ws = d_ws; pc.ws_bytes = ws_part; pc.n = n; pc.st = cl.s;
+    pc.flags = B200SORT_FLAG_NO_SKIP; pc.xf = xf; pc.splitters = spl; pc.nsplit = MAX_SPLITTERS;
+    pc.hist_copy = reinterpret_cast<unsigned long long*>(d_counts); pc.hist_copy_words = PIPE_GROUPS;
+    pc.phase = SortCall::PHASE_COUNT_BEGIN;
+    if ((rc = front_by_width<FAM_PARTITION>(kb, pc))) return rc;
+    for (int c = 0; c < CHUNKS; ++c) {
+        const size_t off = (size_t)c * per_chunk;
+        if (off >= n) break;
+        CU(cudaStreamWaitEvent(cl.s, landed[c], 0));
+        pc.phase = SortCall::PHASE_COUNT_PART; pc.part_off = off; pc.part_n = std::min(per_chunk, n - off);
+        if ((rc = front_by_width<FAM_PARTITION>(kb, pc))) return rc;
+    }
+    tr.mark("per-chunk counts enqueued");
+    if (tr.on) { cudaStreamSynchronize(cl.c); tr.mark("copy-in done"); }
+    pc.phase = SortCall::PHASE_COUNT_END;
+    if ((rc = front_by_width<FAM_PARTITION>(kb, pc))) return rc;
+    pc.phase = SortCall::PHASE_SCATTER;
+    if ((rc = front_by_width<FAM_PARTITION>(kb, pc))) return rc;
     uint64_t counts[PIPE_GROUPS];
     CU(cudaMemcpyAsync(counts, d_counts, sizeof(counts), cudaMemcpyDeviceToHost, cl.s));
     CU(cudaStreamSynchronize(cl.s));

@@ -69,8 +69,12 @@ int sort_front(const SortCall& c) {
     cudaStream_t st = c.st;
     typename Tr::Params prm;
     if (int rc = make_params<FAM, W>(c, &prm)) return rc;
-    const bool do_count = c.phase != SortCall::PHASE_SCATTER;
-    const bool do_scatter = c.phase != SortCall::PHASE_COUNT;
+    const int ph = c.phase;
+    const bool do_zero = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT || ph == SortCall::PHASE_COUNT_BEGIN;
+    const bool do_hist = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT || ph == SortCall::PHASE_COUNT_PART;
+    const bool do_plan = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT || ph == SortCall::PHASE_COUNT_END;
+    const bool do_scatter = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_SCATTER;
+    const bool do_count = do_plan;  // the call that delivers the counts
     if (n == 0) {
         if (c.hist_copy && do_count) B200_CU(cudaMemsetAsync(c.hist_copy, 0, (size_t)c.hist_copy_words * 8, st));
         return B200SORT_OK;
@@ -105,10 +109,14 @@ int sort_front(const SortCall& c) {
 
     PhaseTimer timer(c.out_ms != nullptr, st);
     timer.mark();
-    if (do_count) B200_CU(cudaMemsetAsync(ws + L.zero_off, 0, L.zero_bytes, st));
+    if (do_zero) B200_CU(cudaMemsetAsync(ws + L.zero_off, 0, L.zero_bytes, st));
 
     // K1: one read, all digit histograms
-    if (do_count) {
+    if (do_hist) {
+        const bool part = ph == SortCall::PHASE_COUNT_PART;
+        if (part && c.part_off + c.part_n > n) return fail(B200SORT_ERR_INVALID_ARG, "histogram range outside the keys");
+        const E* h_elems = d_elems + (part ? c.part_off : 0);
+        const size_t h_n = part ? c.part_n : n;
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -121,17 +129,19 @@ int sort_front(const SortCall& c) {
             configured.fetch_or(1u << (dev & 31), std::memory_order_release);
         }
         const size_t per_sm = std::max<size_t>(1, std::min<size_t>(2048 / HT, (220 * 1024) / HS));
-        const size_t vecs = (n * W + 15) / 16;
+        const size_t vecs = (h_n * W + 15) / 16;
         size_t blocks = (vecs + (size_t)HT * 4 - 1) / ((size_t)HT * 4);
         const size_t cap = (size_t)sms * per_sm;
         if (blocks > cap) blocks = cap;
         if (blocks < 1) blocks = 1;
-        hk<<<(unsigned)blocks, HT, HS, st>>>(d_elems, n, hist, prm);
-        count_launch();
-        B200_CU(cudaGetLastError());
+        if (h_n) {
+            hk<<<(unsigned)blocks, HT, HS, st>>>(h_elems, h_n, hist, prm);
+            count_launch();
+            B200_CU(cudaGetLastError());
+        }
     }
     timer.mark();
-    if (do_count) {
+    if (do_plan) {
         if (c.hist_copy)
             B200_CU(cudaMemcpyAsync(c.hist_copy, hist, (size_t)c.hist_copy_words * 8, cudaMemcpyDeviceToDevice, st));
         // K2: bucket bases + pass plan

@@ -212,8 +212,12 @@ struct SortCall {
     //   PHASE_COUNT   memset + K1 + K2: leaves histogram, plan and look-back state in ws
     //   PHASE_SCATTER K3 only, on the state PHASE_COUNT left in the same ws; bucket r goes to
     //                 peer_bases[r] (peer memory) starting at element peer_offsets[r]
-    enum { PHASE_ALL = 0, PHASE_COUNT = 1, PHASE_SCATTER = 2 };
+    //   PHASE_COUNT_BEGIN / _PART / _END: PHASE_COUNT in pieces -- zero the state, histogram
+    //                 elements [part_off, part_off + part_n) (any number of times), then scan + plan;
+    //                 lets the host path count chunks while later chunks are still being copied in
+    enum { PHASE_ALL = 0, PHASE_COUNT = 1, PHASE_SCATTER = 2, PHASE_COUNT_BEGIN = 3, PHASE_COUNT_PART = 4, PHASE_COUNT_END = 5 };
     int phase = PHASE_ALL;
+    size_t part_off = 0, part_n = 0;
     void* const* peer_bases = nullptr;               // host array, nsplit + 1 device pointers
     const unsigned long long* peer_offsets = nullptr;  // device array, nsplit + 1 element offsets
 };
