@@ -62,6 +62,25 @@ def test_pairs_are_stable():
             assert _ref.same_bits(b, want)
 
 
+@pytest.mark.parametrize("kind", _ref.KINDS)
+def test_oracle_matches_committed_golden_fixtures(kind):
+    """tests/golden/<kind>.json: fixed inputs (specials, duplicates, small magnitudes) and the
+    order the reference's tests assert, stated with Python big ints (make_golden.py)."""
+    inp, want = _ref.golden(kind)
+    assert _ref.same_bits(_ref.expected_sorted(inp, kind), want), "numpy statement disagrees with the fixture"
+    for fn in (cpu_oracle.sort0, lambda b, k: cpu_oracle.sort_mt(b, k, 3), lambda b, k: cpu_oracle.sort4_mt(b, k, 3)):
+        b = inp.copy()
+        fn(b, kind)
+        assert _ref.same_bits(b, want)
+
+
+def test_oracle_matches_golden_pairs():
+    inp, want = _ref.golden_pairs()
+    b = inp.copy()
+    cpu_oracle.sort0(b, "pair_u32")
+    assert _ref.same_bits(b, want)
+
+
 F32_ORDER = [  # SURVEY.md 8(c): required ascending order, (bits, ordered key)
     (0xFFC00000, 0x003FFFFF), (0xFF800001, 0x007FFFFE), (0xFF800000, 0x007FFFFF), (0xBF800000, 0x407FFFFF),
     (0x80000001, 0x7FFFFFFE), (0x80000000, 0x7FFFFFFF), (0x00000000, 0x80000000), (0x00000001, 0x80000001),

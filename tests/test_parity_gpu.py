@@ -98,6 +98,27 @@ def test_device_path_edge_sizes(kind, cuda):
 
 
 @pytest.mark.parametrize("kind", _ref.KINDS)
+def test_golden_fixtures(kind, cuda):
+    """The committed fixtures of tests/golden/ through the C ABI: host slice and device buffer."""
+    import torch
+    inp, want = _ref.golden(kind)
+    got = inp.copy()
+    rs.radix_sort(got, _kind(kind))
+    assert _ref.same_bits(got, want), "host path"
+    t = _to_device(inp, cuda)
+    rs.radix_sort(t, _kind(kind))
+    torch.cuda.synchronize()
+    assert _ref.same_bits(t.cpu().numpy(), want), "device path"
+
+
+def test_golden_pairs(cuda):
+    inp, want = _ref.golden_pairs()
+    got = inp.copy()
+    rs.radix_sort_records(got, "u32", 0)
+    assert _ref.same_bits(got, want)
+
+
+@pytest.mark.parametrize("kind", _ref.KINDS)
 def test_host_path_small_and_odd(kind, cuda):
     for n in (1, 2, 97, 1_000_001):
         _check_host(_ref.random_keys(kind, n, seed=n + 7), kind)
