@@ -386,6 +386,13 @@ def run_gpu(args):
                           f"RadixSort::radix_sort (mod.rs:61-176) = {res['radix_sort']:.4f} Gkeys/s; of the rayon variant "
                           f"radix_sort4 (mod.rs:405-466) = {res['radix_sort4']:.4f} Gkeys/s; {cores} host threads")}
 
+    # NVLink roofline of the exchange (rank 0's phase time): every rank sends (world-1)/world of its keys
+    nvlink = None
+    xms = phases.get("exchange") or phases.get("all_to_all")
+    if world > 1 and xms:
+        sent = (world - 1) / world * n * KEY_BYTES
+        nvlink = {"sent_bytes_per_gpu": int(sent), "exchange_ms": round(xms, 3), "GBps_per_direction": round(sent / (xms * 1e-3) / 1e9, 1),
+                  "frac_of_900": round(sent / (xms * 1e-3) / 1e9 / 900.0, 3)}
     line = {
         "metric": "sorted Gkeys/s (u64)", "value": round(value, 3), "unit": "Gkeys/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4),
@@ -394,6 +401,7 @@ def run_gpu(args):
                                 f"uniform random u64 keys, {n} per GPU x {world} GPUs, sharded; MSD splitters + exchange + local LSD "
                                 "(weak-scaled form of BASELINE.json configs[4])"),
                    "exchange": exchange_note, "phases_ms_rank0": {k_: round(v_, 3) for k_, v_ in phases.items()},
+                   "nvlink": nvlink,
                    "keys_per_gpu": n, "seed": SEED, "digits": DIGITS, "digit_bits": 8,
                    "l2": "inputs (8 GB/GPU) exceed the 126 MB L2; no flush between steps",
                    "e2e_steps": e2e_steps, "verified": "sorted + multiset fingerprint == input (bit-identical to the reference's output)"},
