@@ -4,6 +4,8 @@
 // There is deliberately no CPU path: every call launches the sm_100a kernels or
 // returns an error.
 #pragma once
+#include <cstring>
+
 #include "sort_impl.cuh"
 
 namespace b200 {
@@ -46,6 +48,7 @@ int make_params(const SortCall& c, typename FamilyTraits<FAM, W>::type::Params* 
         p.xf = c.xf;
         const U* raw = static_cast<const U*>(c.splitters);
         for (int j = 0; j < c.nsplit; ++j) p.spl[j] = to_ordered_rt<U>(raw[j], c.xf);
+        for (int j = c.nsplit; j < MAX_SPLITTERS; ++j) std::memset(&p.spl[j], 0xFF, sizeof(U));  // padding: largest ordered value
         for (int j = 1; j < c.nsplit; ++j)
             if (ordered_less<U>(p.spl[j], p.spl[j - 1])) return fail(B200SORT_ERR_INVALID_ARG, "splitters are not ascending");
         if (c.peer_bases)

@@ -195,12 +195,35 @@ struct PartitionTraits {
     __device__ __forceinline__ static elem_t xform_out(elem_t e, const Params&) { return e; }
     __device__ __forceinline__ static unsigned digit(elem_t e, int, const Params& p) {
         const U k = to_ordered_rt<U>(e, p.xf);
-        unsigned r = 0;
-        // warp-uniform trip count: 2 GPUs cost one compare per key, not fifteen
+        if (p.nsplit <= 3) {
+            // warp-uniform trip count: 2 GPUs cost one compare per key
+            unsigned r = 0;
 #pragma unroll 1
-        for (int j = 0; j < p.nsplit; ++j)
-            if (!ordered_less<U>(k, p.spl[j])) ++r;
-        return r;
+            for (int j = 0; j < p.nsplit; ++j)
+                if (!ordered_less<U>(k, p.spl[j])) ++r;
+            return r;
+        }
+        // 4..15 splitters: branch-free binary search, four compares; the probe of every
+        // level is picked by selects among kernel-parameter constants (no indexed
+        // loads).  spl[nsplit..14] hold the largest ordered value, so the count can
+        // only overshoot for keys equal to it, and is clamped.
+        const bool b3 = !ordered_less<U>(k, p.spl[7]);
+        U c = b3 ? p.spl[11] : p.spl[3];
+        const bool b2 = !ordered_less<U>(k, c);
+        const U c0 = b2 ? p.spl[5] : p.spl[1];
+        const U c1 = b2 ? p.spl[13] : p.spl[9];
+        c = b3 ? c1 : c0;
+        const bool b1 = !ordered_less<U>(k, c);
+        const U d00 = b1 ? p.spl[2] : p.spl[0];
+        const U d01 = b1 ? p.spl[6] : p.spl[4];
+        const U d10 = b1 ? p.spl[10] : p.spl[8];
+        const U d11 = b1 ? p.spl[14] : p.spl[12];
+        const U e0 = b2 ? d01 : d00;
+        const U e1 = b2 ? d11 : d10;
+        c = b3 ? e1 : e0;
+        const bool b0 = !ordered_less<U>(k, c);
+        const unsigned r = (b3 ? 8u : 0u) + (b2 ? 4u : 0u) + (b1 ? 2u : 0u) + (b0 ? 1u : 0u);
+        return min(r, (unsigned)p.nsplit);
     }
     __device__ __forceinline__ static unsigned long long dst_base(unsigned d, const void* dst, const Params& p) {
         const unsigned long long peer = d <= (unsigned)MAX_SPLITTERS ? p.peer[d] : 0ull;

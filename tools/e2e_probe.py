@@ -44,3 +44,15 @@ for name, thr in (("plain", 2**63), ("pipelined", 0)):
         _ffi.check(L.b200sort_keys_host(host.data_ptr(), n, int(K)))
         best = min(best, time.perf_counter() - t)
     print(name, "keys_host ms", round(best * 1e3, 2), "Gkeys/s", round(n / best / 1e9, 3))
+
+# pageable host memory (what a Rust Vec is): the same call on an unpinned numpy array
+import numpy as np
+rs.set_host_pipeline_min_bytes(64 << 20)
+m = min(n, 500_000_000)
+a = src[:m].cpu().numpy().copy()
+for _ in range(2):
+    b = a.copy()
+    t = time.perf_counter()
+    _ffi.check(L.b200sort_keys_host(b.ctypes.data, m, int(K)))
+    dt = time.perf_counter() - t
+print("pageable keys_host ms", round(dt * 1e3, 2), "Gkeys/s", round(m / dt / 1e9, 3), "(n =", m, ")")
