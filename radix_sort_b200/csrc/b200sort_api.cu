@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "sort_impl.cuh"
+#include "host_staging.cuh"
 
 using namespace b200;
 
@@ -239,16 +240,25 @@ int keys_host_pipelined(void* host, size_t n, int kind) {
     if (rc) return rc;
     struct Cleanup {
         void* block; void* extra = nullptr; cudaStream_t s = nullptr, c = nullptr; cudaEvent_t ev[PIPE_GROUPS] = {};
+        Bounce bounce; bool have_bounce = false;
         ~Cleanup() {
             if (s) cudaStreamSynchronize(s);
             if (c) cudaStreamSynchronize(c);
             for (auto e : ev) if (e) cudaEventDestroy(e);
             if (s) cudaStreamDestroy(s);
             if (c) cudaStreamDestroy(c);
+            if (have_bounce) bounce_release(bounce);
             if (extra) pool_release(extra);
             pool_release(block);
         }
     } cl{block};
+    // a pageable slice (a plain Vec<T>) goes through pinned bounce buffers filled and
+    // emptied by the library's copy threads (host_staging.cuh); a pinned one is DMA'd directly
+    const bool staged = is_pageable(host);
+    if (staged) {
+        CU(bounce_acquire(&cl.bounce));
+        cl.have_bounce = true;
+    }
     CU(cudaStreamCreateWithFlags(&cl.s, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&cl.c, cudaStreamNonBlocking));
     unsigned char* d_in = static_cast<unsigned char*>(block);
@@ -265,15 +275,17 @@ int keys_host_pipelined(void* host, size_t n, int kind) {
     const size_t per_chunk = ((n + CHUNKS - 1) / CHUNKS + 4095) / 4096 * 4096;  // whole 16-byte vectors for K1
     cudaEvent_t landed[CHUNKS] = {};
     struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < CHUNKS; ++i) if (e[i]) cudaEventDestroy(e[i]); } } eg{landed};
-    for (int c = 0; c < CHUNKS; ++c) {
-        const size_t off = (size_t)c * per_chunk;
-        if (off >= n) break;
-        const size_t cnt = std::min(per_chunk, n - off);
-        CU(cudaMemcpyAsync(d_in + off * kb, static_cast<const unsigned char*>(host) + off * kb, cnt * kb, cudaMemcpyHostToDevice, cl.c));
-        CU(cudaEventCreateWithFlags(&landed[c], cudaEventDisableTiming));
-        CU(cudaEventRecord(landed[c], cl.c));
+    if (!staged) {
+        for (int c = 0; c < CHUNKS; ++c) {
+            const size_t off = (size_t)c * per_chunk;
+            if (off >= n) break;
+            const size_t cnt = std::min(per_chunk, n - off);
+            CU(cudaMemcpyAsync(d_in + off * kb, static_cast<const unsigned char*>(host) + off * kb, cnt * kb, cudaMemcpyHostToDevice, cl.c));
+            CU(cudaEventCreateWithFlags(&landed[c], cudaEventDisableTiming));
+            CU(cudaEventRecord(landed[c], cl.c));
+        }
+        tr.mark("copy-in enqueued");
     }
-    tr.mark("copy-in enqueued");
     alignas(16) unsigned char spl[MAX_SPLITTERS * 16];
     const int xf = kind_xf(kind);
     switch (kb) {
@@ -290,11 +302,19 @@ int keys_host_pipelined(void* host, size_t n, int kind) {
     pc.hist_copy = reinterpret_cast<unsigned long long*>(d_counts); pc.hist_copy_words = PIPE_GROUPS;
     pc.phase = SortCall::PHASE_COUNT_BEGIN;
     if ((rc = front_by_width<FAM_PARTITION>(kb, pc))) return rc;
+    size_t bounce_issued = 0;
     for (int c = 0; c < CHUNKS; ++c) {
         const size_t off = (size_t)c * per_chunk;
         if (off >= n) break;
+        const size_t cnt = std::min(per_chunk, n - off);
+        if (staged) {  // the host thread feeds the bounce buffers; the counts of chunk c run under the copy of chunk c + 1
+            CU(staged_copy_in(cl.bounce, d_in + off * kb, static_cast<const unsigned char*>(host) + off * kb, cnt * kb, cl.c,
+                              &bounce_issued));
+            CU(cudaEventCreateWithFlags(&landed[c], cudaEventDisableTiming));
+            CU(cudaEventRecord(landed[c], cl.c));
+        }
         CU(cudaStreamWaitEvent(cl.s, landed[c], 0));
-        pc.phase = SortCall::PHASE_COUNT_PART; pc.part_off = off; pc.part_n = std::min(per_chunk, n - off);
+        pc.phase = SortCall::PHASE_COUNT_PART; pc.part_off = off; pc.part_n = cnt;
         if ((rc = front_by_width<FAM_PARTITION>(kb, pc))) return rc;
     }
     tr.mark("per-chunk counts enqueued");
@@ -321,19 +341,28 @@ int keys_host_pipelined(void* host, size_t n, int kind) {
         ws_sort_bytes = need;
     }
     size_t off = 0;
-    for (int g = 0; g < PIPE_GROUPS; ++g) {
+    for (int g = 0; g < PIPE_GROUPS; ++g) {  // all range sorts first: they are asynchronous
         const size_t cnt = (size_t)counts[g];
         if (cnt == 0) continue;
         rc = keys_device_dispatch(d_out + off * kb, ws_sort, ws_sort_bytes, cnt, kind, cl.s, 0, nullptr, 0);
         if (rc) return rc;
         CU(cudaEventCreateWithFlags(&cl.ev[g], cudaEventDisableTiming));
         CU(cudaEventRecord(cl.ev[g], cl.s));
-        CU(cudaStreamWaitEvent(cl.c, cl.ev[g], 0));
-        CU(cudaMemcpyAsync(static_cast<unsigned char*>(host) + off * kb, d_out + off * kb, cnt * kb, cudaMemcpyDeviceToHost, cl.c));
         off += cnt;
     }
     if (off != n) return fail(B200SORT_ERR_CUDA, "partition counts do not add up to n");
-    tr.mark("range sorts + copy-outs enqueued");
+    tr.mark("range sorts enqueued");
+    StagedCopyOut out(cl.bounce, cl.c);
+    off = 0;
+    for (int g = 0; g < PIPE_GROUPS; ++g) {  // then the copy-outs, each behind its range's sort
+        const size_t cnt = (size_t)counts[g];
+        if (cnt == 0) continue;
+        CU(cudaStreamWaitEvent(cl.c, cl.ev[g], 0));
+        if (staged) CU(out.add(static_cast<unsigned char*>(host) + off * kb, d_out + off * kb, cnt * kb));
+        else CU(cudaMemcpyAsync(static_cast<unsigned char*>(host) + off * kb, d_out + off * kb, cnt * kb, cudaMemcpyDeviceToHost, cl.c));
+        off += cnt;
+    }
+    if (staged) CU(out.finish());
     CU(cudaStreamSynchronize(cl.s));
     tr.mark("range sorts done");
     CU(cudaStreamSynchronize(cl.c));

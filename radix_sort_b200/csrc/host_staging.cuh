@@ -1,0 +1,218 @@
+// host_staging.cuh -- moving a PAGEABLE host slice (what a Rust Vec<T> is) to and
+// from the device at PCIe speed.
+//
+// cudaMemcpyAsync on pageable memory is staged by the driver through one pinned
+// buffer by one thread: 13-15 GB/s on the B200 boxes, a quarter of the link
+// (r01: 1 B u64 keys end to end 1240 ms pageable vs 294 ms pinned).  Pinning the
+// caller's slice for the call (cudaHostRegister) costs more than it saves.  So
+// the library owns a few pinned bounce buffers and a small pool of copy threads:
+// chunk k is copied slice -> bounce by the threads while the DMA of chunk k-1
+// runs, and the other way round on the way out.
+//
+// Replaces nothing in the reference (its slices never leave the host); it is the
+// host half of the drop-in boundary b200sort_keys_host.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <condition_variable>
+#include <cstring>
+#include <deque>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+namespace b200 {
+
+// ---- persistent copy threads: memcpy split into one slice per thread ---------------
+class CopyPool {
+public:
+    static CopyPool& get() {
+        static CopyPool p;
+        return p;
+    }
+    void copy(void* dst, const void* src, size_t bytes) {
+        if (bytes < ((size_t)1 << 20) || workers_.empty()) {
+            std::memcpy(dst, src, bytes);
+            return;
+        }
+        std::lock_guard<std::mutex> one_job(submit_);
+        const int parts = (int)workers_.size() + 1;
+        const size_t per = ((bytes + parts - 1) / parts + 63) / 64 * 64;
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            dst_ = static_cast<unsigned char*>(dst);
+            src_ = static_cast<const unsigned char*>(src);
+            bytes_ = bytes;
+            per_ = per;
+            pending_ = (int)workers_.size();
+            ++generation_;
+        }
+        cv_.notify_all();
+        slice(parts - 1);  // the caller copies the last slice itself
+        std::unique_lock<std::mutex> lk(mu_);
+        done_.wait(lk, [&] { return pending_ == 0; });
+    }
+
+private:
+    CopyPool() {
+        unsigned hc = std::thread::hardware_concurrency();
+        int n = hc ? (int)hc / 2 : 4;
+        n = std::max(1, std::min(n, 7));
+        for (int i = 0; i < n; ++i) workers_.emplace_back([this, i] { run(i); });
+    }
+    ~CopyPool() {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        for (auto& t : workers_) t.join();
+    }
+    void slice(int i) {
+        const size_t off = (size_t)i * per_;
+        if (off < bytes_) std::memcpy(dst_ + off, src_ + off, std::min(per_, bytes_ - off));
+    }
+    void run(int i) {
+        unsigned long long seen = 0;
+        for (;;) {
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return stop_ || generation_ != seen; });
+                if (stop_) return;
+                seen = generation_;
+            }
+            slice(i);
+            std::lock_guard<std::mutex> lk(mu_);
+            if (--pending_ == 0) done_.notify_one();
+        }
+    }
+    std::vector<std::thread> workers_;
+    std::mutex submit_, mu_;
+    std::condition_variable cv_, done_;
+    unsigned char* dst_ = nullptr;
+    const unsigned char* src_ = nullptr;
+    size_t bytes_ = 0, per_ = 0;
+    int pending_ = 0;
+    unsigned long long generation_ = 0;
+    bool stop_ = false;
+};
+
+// ---- pinned bounce buffers, cached process-wide -----------------------------------
+struct Bounce {
+    static constexpr int NBUF = 4;
+    static constexpr size_t BUF = (size_t)16 << 20;
+    unsigned char* base = nullptr;  // NBUF * BUF bytes of pinned memory
+    cudaEvent_t done[NBUF] = {};    // DMA that last used buffer i
+    unsigned char* buf(int i) const { return base + (size_t)i * BUF; }
+};
+
+inline std::mutex& bounce_mu() {
+    static std::mutex m;
+    return m;
+}
+inline std::vector<Bounce>& bounce_free() {
+    static std::vector<Bounce> v;
+    return v;
+}
+inline cudaError_t bounce_acquire(Bounce* out) {
+    {
+        std::lock_guard<std::mutex> lk(bounce_mu());
+        if (!bounce_free().empty()) {
+            *out = bounce_free().back();
+            bounce_free().pop_back();
+            return cudaSuccess;
+        }
+    }
+    Bounce b;
+    cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&b.base), Bounce::NBUF * Bounce::BUF, cudaHostAllocDefault);
+    if (e != cudaSuccess) return e;
+    for (int i = 0; i < Bounce::NBUF; ++i) {
+        e = cudaEventCreateWithFlags(&b.done[i], cudaEventDisableTiming);
+        if (e != cudaSuccess) return e;
+    }
+    *out = b;
+    return cudaSuccess;
+}
+inline void bounce_release(const Bounce& b) {
+    std::lock_guard<std::mutex> lk(bounce_mu());
+    bounce_free().push_back(b);
+}
+
+// true when the driver does not know `p` as pinned / registered host memory
+inline bool is_pageable(const void* p) {
+    cudaPointerAttributes a{};
+    const cudaError_t e = cudaPointerGetAttributes(&a, p);
+    if (e != cudaSuccess) {
+        cudaGetLastError();  // older drivers report unregistered memory as an error: not one for us
+        return true;
+    }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+
+// slice [host, host + bytes) -> device, through the bounce buffers, on stream `st`.
+// Returns with every DMA enqueued (the last NBUF may still be running).
+inline cudaError_t staged_copy_in(const Bounce& b, unsigned char* d_dst, const unsigned char* host, size_t bytes,
+                                  cudaStream_t st, size_t* issued) {
+    for (size_t off = 0; off < bytes; off += Bounce::BUF, ++*issued) {
+        const int i = (int)(*issued % Bounce::NBUF);
+        const size_t len = std::min(Bounce::BUF, bytes - off);
+        if (*issued >= (size_t)Bounce::NBUF) {
+            const cudaError_t e = cudaEventSynchronize(b.done[i]);
+            if (e != cudaSuccess) return e;
+        }
+        CopyPool::get().copy(b.buf(i), host + off, len);
+        cudaError_t e = cudaMemcpyAsync(d_dst + off, b.buf(i), len, cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) return e;
+        e = cudaEventRecord(b.done[i], st);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+// device -> slice through the bounce buffers: DMAs are issued up to NBUF ahead of the
+// host copies that empty the buffers, in order.
+class StagedCopyOut {
+public:
+    StagedCopyOut(const Bounce& b, cudaStream_t st) : b_(b), st_(st) {}
+    cudaError_t add(unsigned char* host, const unsigned char* d_src, size_t bytes) {
+        for (size_t off = 0; off < bytes; off += Bounce::BUF, ++issued_) {
+            if (q_.size() == (size_t)Bounce::NBUF) {
+                const cudaError_t e = drain_one();
+                if (e != cudaSuccess) return e;
+            }
+            const int i = (int)(issued_ % Bounce::NBUF);
+            const size_t len = std::min(Bounce::BUF, bytes - off);
+            cudaError_t e = cudaMemcpyAsync(b_.buf(i), d_src + off, len, cudaMemcpyDeviceToHost, st_);
+            if (e != cudaSuccess) return e;
+            e = cudaEventRecord(b_.done[i], st_);
+            if (e != cudaSuccess) return e;
+            q_.push_back({i, host + off, len});
+        }
+        return cudaSuccess;
+    }
+    cudaError_t finish() {
+        while (!q_.empty()) {
+            const cudaError_t e = drain_one();
+            if (e != cudaSuccess) return e;
+        }
+        return cudaSuccess;
+    }
+
+private:
+    struct Pending { int buf; unsigned char* host; size_t len; };
+    cudaError_t drain_one() {
+        const Pending p = q_.front();
+        q_.pop_front();
+        const cudaError_t e = cudaEventSynchronize(b_.done[p.buf]);
+        if (e != cudaSuccess) return e;
+        CopyPool::get().copy(p.host, b_.buf(p.buf), p.len);
+        return cudaSuccess;
+    }
+    const Bounce& b_;
+    cudaStream_t st_;
+    std::deque<Pending> q_;
+    size_t issued_ = 0;
+};
+
+}  // namespace b200
