@@ -177,12 +177,32 @@ int host_roundtrip(void* host, size_t bytes, size_t ws_bytes, SortFn sort) {
     cudaError_t e = cudaStreamCreateWithFlags(&sg.st, cudaStreamNonBlocking);
     if (e != cudaSuccess) { pool_release(block); return cuda_fail(e, "cudaStreamCreate"); }
     unsigned char* d = static_cast<unsigned char*>(block);
-    e = cudaMemcpyAsync(d, host, bytes, cudaMemcpyHostToDevice, sg.st);
+    // large pageable slices (a plain Vec<T>) go through the library's pinned bounce
+    // buffers and copy threads (host_staging.cuh); everything else is one DMA each way
+    Bounce bounce;
+    const bool staged = bytes >= ((size_t)64 << 20) && is_pageable(host);
+    if (staged) e = bounce_acquire(&bounce);
+    if (e != cudaSuccess) { pool_release(block); return cuda_fail(e, "cudaHostAlloc(bounce buffers)"); }
+    if (staged) {
+        size_t issued = 0;
+        e = staged_copy_in(bounce, d, static_cast<const unsigned char*>(host), bytes, sg.st, &issued);
+    } else {
+        e = cudaMemcpyAsync(d, host, bytes, cudaMemcpyHostToDevice, sg.st);
+    }
     if (e == cudaSuccess) {
         rc = sort(d, d + data_bytes, ws_bytes, sg.st);
-        if (rc == B200SORT_OK) e = cudaMemcpyAsync(host, d, bytes, cudaMemcpyDeviceToHost, sg.st);
+        if (rc == B200SORT_OK) {
+            if (staged) {
+                StagedCopyOut out(bounce, sg.st);
+                e = out.add(static_cast<unsigned char*>(host), d, bytes);
+                if (e == cudaSuccess) e = out.finish();
+            } else {
+                e = cudaMemcpyAsync(host, d, bytes, cudaMemcpyDeviceToHost, sg.st);
+            }
+        }
     }
     const cudaError_t e2 = cudaStreamSynchronize(sg.st);
+    if (staged) bounce_release(bounce);
     pool_release(block);
     if (rc) return rc;
     if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync");
