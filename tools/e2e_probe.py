@@ -56,3 +56,15 @@ for _ in range(2):
     _ffi.check(L.b200sort_keys_host(b.ctypes.data, m, int(K)))
     dt = time.perf_counter() - t
 print("pageable keys_host ms", round(dt * 1e3, 2), "Gkeys/s", round(m / dt / 1e9, 3), "(n =", m, ")")
+
+# pageable (key, value) records: the demo's (u32,u32) and (u64,u64) shapes (main.rs:108-125)
+for kind, rec_dtype, mrec in ((rs.Kind.U32, np.uint32, min(n // 2, 500_000_000)), (rs.Kind.U64, np.uint64, min(n // 4, 250_000_000))):
+    rng = np.random.default_rng(3)
+    recs = rng.integers(0, np.iinfo(rec_dtype).max, size=(mrec, 2), dtype=rec_dtype)
+    for _ in range(2):
+        b = recs.copy()
+        t = time.perf_counter()
+        rs.radix_sort_records(b, kind, key_off=0)
+        dt = time.perf_counter() - t
+    ok = bool((b[1:, 0] >= b[:-1, 0]).all())
+    print("pageable records", rec_dtype.__name__, "ms", round(dt * 1e3, 2), "Grec/s", round(mrec / dt / 1e9, 3), "sorted", ok, "(n =", mrec, ")")
