@@ -62,10 +62,10 @@ template <int FAM, int W> struct Variants;
 template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}, {3, 512, 32, 2, 0}, {1, 448, 32, 2, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_2 3
 template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}, {3, 512, 24, 2, 0}, {1, 448, 24, 2, 64}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_KEYS_4 5
-template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 22, 2, 0}, {3, 512, 22, 2, 0}, {0, 512, 16, 2, 0}, {1, 384, 20, 2, 128}, {2, 384, 16, 2, 128}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_KEYS_8 5
-template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {3, 512, 16, 2, 0}, {0, 512, 12, 2, 0}, {1, 384, 12, 2, 128}, {2, 384, 10, 2, 128}}; static constexpr int FALLBACK = 0; };
+#define B200_NV_KEYS_4 10
+template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 22, 2, 0}, {3, 512, 22, 2, 0}, {0, 512, 16, 2, 0}, {1, 384, 20, 2, 128}, {2, 384, 16, 2, 128}, {0, 512, 22, 2, 16}, {0, 512, 22, 2, 4}, {3, 512, 22, 2, 16}, {0, 512, 22, 2, 12}, {3, 512, 22, 2, 4}}; static constexpr int FALLBACK = 0; };
+#define B200_NV_KEYS_8 10
+template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {3, 512, 16, 2, 0}, {0, 512, 12, 2, 0}, {1, 384, 12, 2, 128}, {2, 384, 10, 2, 128}, {0, 512, 16, 2, 16}, {0, 512, 16, 2, 4}, {3, 512, 16, 2, 16}, {0, 512, 16, 2, 12}, {0, 512, 16, 2, 24}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_KEYS_16 3
 template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {3, 256, 12, 2, 0}, {1, 256, 8, 3, 64}}; static constexpr int FALLBACK = 0; };
 #define B200_NV_RECORDS_8 3

@@ -342,6 +342,17 @@ __device__ __forceinline__ void column_bases(uint32_t* warp_hist, int d, uint32_
     }
 }
 
+// Make the compiler forget what it knows about a key (no instruction is emitted).
+// Without this it keeps every key's counter ADDRESS from the count phase alive for
+// the scatter phase -- ITEMS extra registers, which at the 64-register cap end up in
+// local memory (STL/LDL in the hot loop: more LSU traffic on an LSU-bound kernel).
+// Recomputing shift + mask + add per key is cheaper.
+__device__ __forceinline__ void launder(unsigned char& v) { unsigned t = v; asm volatile("" : "+r"(t)); v = (unsigned char)t; }
+__device__ __forceinline__ void launder(unsigned short& v) { asm volatile("" : "+h"(v)); }
+__device__ __forceinline__ void launder(unsigned int& v) { asm volatile("" : "+r"(v)); }
+__device__ __forceinline__ void launder(unsigned long long& v) { asm volatile("" : "+l"(v)); }
+__device__ __forceinline__ void launder(u128& v) { asm volatile("" : "+l"(v.lo), "+l"(v.hi)); }
+
 // ---- named barriers (bar.sync / bar.arrive id, count): the persistent kernel
 // splits its CTA into worker warps and look-back warps that meet only at the
 // hand-over points, so the CTA-wide barrier 0 cannot be used inside the tile loop
@@ -394,23 +405,30 @@ struct LookBack {
         for (int j = 0; j < B; ++j)
             v[j] = (pos - j >= 0) ? ld_relaxed_u32(p - (size_t)j * RADIX) : LB_FLAG_INCLUSIVE;
     }
-    // sum of the counts of all preceding tiles
+    // sum of the counts of all preceding tiles.  Branch-free inside a batch: the walk is
+    // a serial chain run by 8 of the CTA's 16 warps while the others wait at the
+    // barrier (r01 ncu, u64: a quarter of the tile's wall time, most of it the
+    // per-word branches, not the round trips), so a batch costs a handful of
+    // selects per word and ONE branch.  A batch that holds an unpublished word in
+    // front of its first INCLUSIVE word is asked for again as a whole.
     __device__ __forceinline__ uint32_t resolve(const uint32_t* p, int pos) {
         uint32_t sum = 0;
         for (;;) {
-            bool done = false;
+            uint32_t part = 0;
+            bool open = true, ok = true;
 #pragma unroll
             for (int j = 0; j < B; ++j) {
-                if (!done) {
-                    uint32_t x = v[j];
-                    while ((x & (LB_FLAG_PARTIAL | LB_FLAG_INCLUSIVE)) == 0) x = ld_relaxed_u32(p - (size_t)j * RADIX);
-                    sum += x & LB_VALUE_MASK;
-                    done = (x & LB_FLAG_INCLUSIVE) != 0;
-                }
+                const uint32_t x = v[j];
+                ok &= !open || x >= LB_FLAG_PARTIAL;       // a word of the open range not yet published
+                part += open ? (x & LB_VALUE_MASK) : 0u;
+                open &= (x & LB_FLAG_INCLUSIVE) == 0;
             }
-            if (done) return sum;
-            p -= (size_t)B * RADIX;
-            pos -= B;
+            if (ok) {
+                sum += part;
+                if (!open) return sum;
+                p -= (size_t)B * RADIX;
+                pos -= B;
+            }
             request(p, pos);
         }
     }
@@ -540,6 +558,10 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
             if (FULL || wbase + i * 32 < tile_n) atomicAdd(&my_hist[hidx(Tr::digit(e[i], pass, a.prm))], 1u);
     }
     workers_sync<WORKERS, LBT>();
+    if constexpr (!Tr::NEEDS_STABLE && !Tr::FEW_BUCKETS) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) launder(e[i]);
+    }
     after_count();  // persistent kernel: thread 0 starts the bulk copy of the next tile
 
     // ---- decoupled look-back in line, one digit per thread of the last 256 threads,
@@ -552,10 +574,11 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
         if (tid >= LB0) {
             const int d = tid - LB0;
             const uint32_t cnt_d = sh.cnt[d];
+            const unsigned long long bin_d = a.bins_in[d];  // asked for before the walk: its round trip overlaps the walk's
             unsigned long long excl_tiles = 0;
             if (ABL & 1) {  // timing ablation: no polling, a plausible distinct address
                 excl_tiles = min((unsigned long long)tile * (WORKERS * ITEMS / RADIX),
-                                 (unsigned long long)a.portion_n - cnt_d - min((unsigned long long)a.portion_n - cnt_d, a.bins_in[d]));
+                                 (unsigned long long)a.portion_n - cnt_d - min((unsigned long long)a.portion_n - cnt_d, bin_d));
             } else if (tile > 0) {
                 LookBack<LBB> look;
                 look.request(lb - RADIX + d, (int)tile - 1);
@@ -563,7 +586,7 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
                 st_relaxed_u32(lb + d, LB_FLAG_INCLUSIVE | (sum + cnt_d));
                 excl_tiles = sum;
             }
-            const unsigned long long gbase = a.bins_in[d] + excl_tiles;
+            const unsigned long long gbase = bin_d + excl_tiles;
             sh.gptr[d] = Tr::dst_base((unsigned)d, dst, a.prm) + (gbase - sh.excl[d]) * sizeof(E);
             if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[d] = gbase + cnt_d;
         }
