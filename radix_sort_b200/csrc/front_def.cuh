@@ -90,9 +90,6 @@ int sort_front(const SortCall& c) {
 
     int variant = variant_override(FAM, W);
     if (variant < 0 || variant >= num_variants<FAM, W>()) variant = 0;
-    // the TMA ring of the persistent kernel needs 16-byte aligned tiles
-    const bool aligned16 = ((uintptr_t)d_elems % 16) == 0 && (!c.alt_out || ((uintptr_t)c.alt_out % 16) == 0);
-    if ((Variants<FAM, W>::v[variant].kernel == 1 || Variants<FAM, W>::v[variant].kernel == 2) && !aligned16) variant = Variants<FAM, W>::FALLBACK;
     const VariantDesc vd = Variants<FAM, W>::v[variant];
     const int tile = vd.threads * vd.items;
     const Layout L = make_layout(n, W, D, tile, FAM != FAM_PARTITION);

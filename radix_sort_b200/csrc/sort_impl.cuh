@@ -17,7 +17,6 @@
 
 #include "../../include/b200sort.h"
 #include "sort_kernels.cuh"
-#include "ring_kernel.cuh"
 #include "stream_kernel.cuh"
 
 namespace b200 {
@@ -46,42 +45,41 @@ template <> struct FamilyTraits<FAM_RECORDS, 8> { using type = RecordTraits<unsi
 template <> struct FamilyTraits<FAM_RECORDS, 16> { using type = RecordTraits<u128, unsigned long long>; };
 
 // ---- K3 variants ------------------------------------------------------------------
-// kernel: 0 = onesweep_pass_kernel (one tile per CTA, any alignment)
-//         1 = onesweep_persistent_kernel (two-slot TMA ring, look-back warps; 16-byte aligned buffers)
-//         2 = onesweep_ring_kernel (three-slot TMA ring, deferred write-out; ring_kernel.cuh)
+// kernel: 0 = onesweep_pass_kernel (one tile per CTA)
 //         3 = onesweep_stream_kernel (resident CTAs, next tile's keys prefetched into the dead
-//             key registers; any alignment; stream_kernel.cuh)
+//             key registers; stream_kernel.cuh)
+//         (1 and 2 were the TMA-ring kernels, removed: see sort_kernels.cuh)
 // Index 0 of a table is the default (the fastest measured on B200, profiles/);
-// FALLBACK names the one-tile variant used when a buffer is not 16-byte aligned.  The other entries exist
+// The other entries exist
 // for on-GPU sweeps (b200sort_set_variant).  The counts are repeated as macros
 // because the dispatcher and the build script need them in the preprocessor.
-struct VariantDesc { int kernel, threads, items, min_blocks, lbt; };  // threads = worker threads; lbt = look-back threads (kernel 0: predecessors read per look-back round, 0 = LB_BATCH)
+struct VariantDesc { int kernel, threads, items, min_blocks, lbb; };  // lbb = predecessors read per look-back round (0 = LB_BATCH); bits 8+ = timing-ablation mask
 
 template <int FAM, int W> struct Variants;
-#define B200_NV_KEYS_1 3
-template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}, {3, 512, 32, 2, 0}, {1, 448, 32, 2, 64}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_KEYS_2 3
-template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}, {3, 512, 24, 2, 0}, {1, 448, 24, 2, 64}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_KEYS_4 10
-template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 22, 2, 0}, {3, 512, 22, 2, 0}, {0, 512, 16, 2, 0}, {1, 384, 20, 2, 128}, {2, 384, 16, 2, 128}, {0, 512, 22, 2, 16}, {0, 512, 22, 2, 4}, {3, 512, 22, 2, 16}, {0, 512, 22, 2, 12}, {3, 512, 22, 2, 4}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_KEYS_8 10
-template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {3, 512, 16, 2, 0}, {0, 512, 12, 2, 0}, {1, 384, 12, 2, 128}, {2, 384, 10, 2, 128}, {0, 512, 16, 2, 16}, {0, 512, 16, 2, 4}, {3, 512, 16, 2, 16}, {0, 512, 16, 2, 12}, {0, 512, 16, 2, 24}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_KEYS_16 3
-template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {3, 256, 12, 2, 0}, {1, 256, 8, 3, 64}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_RECORDS_8 3
-template <> struct Variants<FAM_RECORDS, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0}, {3, 512, 12, 2, 0}, {1, 448, 8, 2, 64}}; static constexpr int FALLBACK = 0; };
-#define B200_NV_RECORDS_16 3
-template <> struct Variants<FAM_RECORDS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {3, 256, 12, 2, 0}, {1, 256, 8, 3, 64}}; static constexpr int FALLBACK = 0; };
+#define B200_NV_KEYS_1 2
+template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}, {3, 512, 32, 2, 0}}; };
+#define B200_NV_KEYS_2 2
+template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}, {3, 512, 24, 2, 0}}; };
+#define B200_NV_KEYS_4 3
+template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 22, 2, 0}, {3, 512, 22, 2, 0}, {0, 512, 16, 2, 0}}; };
+#define B200_NV_KEYS_8 3
+template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {3, 512, 16, 2, 0}, {0, 256, 20, 3, 0}}; };
+#define B200_NV_KEYS_16 2
+template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {3, 256, 12, 2, 0}}; };
+#define B200_NV_RECORDS_8 2
+template <> struct Variants<FAM_RECORDS, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0}, {3, 512, 12, 2, 0}}; };
+#define B200_NV_RECORDS_16 2
+template <> struct Variants<FAM_RECORDS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {3, 256, 12, 2, 0}}; };
 #define B200_NV_PARTITION_1 1
-template <> struct Variants<FAM_PARTITION, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_PARTITION, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}}; };
 #define B200_NV_PARTITION_2 1
-template <> struct Variants<FAM_PARTITION, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_PARTITION, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}}; };
 #define B200_NV_PARTITION_4 1
-template <> struct Variants<FAM_PARTITION, 4> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_PARTITION, 4> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}}; };
 #define B200_NV_PARTITION_8 1
-template <> struct Variants<FAM_PARTITION, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_PARTITION, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0}}; };
 #define B200_NV_PARTITION_16 1
-template <> struct Variants<FAM_PARTITION, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}}; static constexpr int FALLBACK = 0; };
+template <> struct Variants<FAM_PARTITION, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}}; };
 
 template <int FAM, int W> constexpr int num_variants() { return (int)(sizeof(Variants<FAM, W>::v) / sizeof(VariantDesc)); }
 
@@ -95,13 +93,12 @@ struct VariantEntry {
 template <typename Tr, int KERNEL, int THREADS, int ITEMS, int MINB, int LBT>
 struct PassLauncher {
     using SM = PassSmem<Tr, THREADS, ITEMS>;
-    static constexpr int BLOCK = THREADS + ((KERNEL == 0 || KERNEL == 3) ? 0 : LBT);  // kernels 0, 3 read lbt as the look-back batch
+    static_assert(KERNEL == 0 || KERNEL == 3, "kernel ids: 0 one tile per CTA, 3 streaming");
+    static constexpr int BLOCK = THREADS;
     static constexpr int LBB = (LBT & 255) > 0 ? (LBT & 255) : LB_BATCH;
-    static constexpr size_t SMEM = KERNEL == 2 ? RingSmem<Tr, THREADS, ITEMS>::TOTAL : KERNEL == 1 ? SM::TOTAL_PERSISTENT : SM::TOTAL;
+    static constexpr size_t SMEM = SM::TOTAL;
     static auto kernel() {
         if constexpr (KERNEL == 3) return onesweep_stream_kernel<Tr, THREADS, ITEMS, MINB, LBB, (LBT >> 8)>;
-        else if constexpr (KERNEL == 2) return onesweep_ring_kernel<Tr, THREADS, ITEMS, LBT, MINB>;
-        else if constexpr (KERNEL == 1) return onesweep_persistent_kernel<Tr, THREADS, ITEMS, LBT, MINB>;
         else return onesweep_pass_kernel<Tr, THREADS, ITEMS, MINB, LBB, (LBT >> 8)>;
     }
     // per-device one-time setup: opt in to the dynamic shared memory, read the occupancy
@@ -132,7 +129,7 @@ struct PassLauncher {
         cudaError_t e = prepare(&resident);
         if (e != cudaSuccess) return e;
         unsigned grid = a.num_tiles;
-        if (KERNEL >= 1 && grid > (unsigned)resident) grid = (unsigned)resident;
+        if (KERNEL == 3 && grid > (unsigned)resident) grid = (unsigned)resident;
         kernel()<<<grid, BLOCK, SMEM, st>>>(a);
         count_launch();
         return cudaGetLastError();

@@ -231,15 +231,14 @@ scan_plan_kernel(const unsigned long long* __restrict__ hist, unsigned long long
 // relaxed loads), and the first batch is requested before the scatter so that it
 // has landed by the time the scatter is done.
 //
-// Two kernels share this tile code:
-//   onesweep_pass_kernel        one tile per CTA, keys loaded straight into
-//                               registers; any alignment; the general path.
-//   onesweep_persistent_kernel  CTAs stay resident and draw tiles from the ticket
-//                               counter; tile i+1 is fetched by a TMA bulk copy
-//                               (cp.async.bulk, completion on an mbarrier) into
-//                               the other half of a two-tile ring while tile i is
-//                               ranked; the ring slot doubles as the digit-sorted
-//                               staging buffer.  Needs 16-byte aligned buffers.
+// Two kernels share this tile code (rank_and_scatter):
+//   onesweep_pass_kernel    one tile per CTA, keys loaded straight into registers.
+//   onesweep_stream_kernel  (stream_kernel.cuh) resident CTAs loop over tickets and
+//                           keep the next tile's loads in flight.
+// Two TMA-ring kernels (cp.async.bulk + mbarrier, look-back in dedicated warps,
+// deferred write-out) were built and measured 10-40 % slower on every width
+// (profiles/r01_sweep_v5*, v13*, v16*); they were removed after commit 1a4e2dd --
+// the polling warps and the second tile buffer cost more than the overlap gained.
 // ---------------------------------------------------------------------------
 template <typename Tr>
 struct PassArgs {
@@ -250,7 +249,7 @@ struct PassArgs {
     unsigned long long portion_off;      // first element of this portion
     uint32_t portion_n;                  // elements in this portion
     uint32_t num_tiles;
-    uint32_t grid;                       // CTAs to launch (persistent kernel: resident CTAs)
+    uint32_t grid;                       // CTAs to launch (streaming kernel: resident CTAs)
     const unsigned long long* bins_in;   // [256] global base of each bucket for this portion
     unsigned long long* bins_out;        // [256] base for the next portion (or null)
     uint32_t* lookback;                  // [num_tiles][256] status words, zeroed
@@ -271,8 +270,7 @@ struct PassSmem {
     static constexpr size_t EXCL_BYTES = (size_t)RADIX * sizeof(uint32_t);
     static constexpr size_t CNT_BYTES = (size_t)RADIX * sizeof(uint32_t);
     static constexpr size_t AUX_BYTES = HIST_BYTES + GPTR_BYTES + EXCL_BYTES + CNT_BYTES + 64 + 16;
-    static constexpr size_t TOTAL = TILE_BYTES + AUX_BYTES;             // one-tile kernel
-    static constexpr size_t TOTAL_PERSISTENT = 2 * TILE_BYTES + AUX_BYTES;  // two-tile ring
+    static constexpr size_t TOTAL = TILE_BYTES + AUX_BYTES;
 };
 
 // views into the dynamic shared memory of one CTA: [tile buffers | aux]
@@ -285,7 +283,6 @@ struct PassShared {
     uint32_t* excl;                 // [256] keys of the tile with a smaller digit
     uint32_t* cnt;                  // [256] keys of the tile with this digit
     uint32_t* misc;                 // [0..1] tickets, [2..9] warp totals of the digit scan
-    unsigned long long* mbar;       // [2] mbarriers of the ring (persistent kernel)
     __device__ __forceinline__ PassShared() {}
     __device__ __forceinline__ PassShared(unsigned char* raw, size_t tile_bytes_total) {
         tile = reinterpret_cast<typename Tr::elem_t*>(raw);
@@ -295,7 +292,6 @@ struct PassShared {
         excl = reinterpret_cast<uint32_t*>(aux + SM::HIST_BYTES + SM::GPTR_BYTES);
         cnt = excl + RADIX;
         misc = cnt + RADIX;
-        mbar = reinterpret_cast<unsigned long long*>(misc + 16);
     }
 };
 
@@ -353,47 +349,6 @@ __device__ __forceinline__ void launder(unsigned int& v) { asm volatile("" : "+r
 __device__ __forceinline__ void launder(unsigned long long& v) { asm volatile("" : "+l"(v)); }
 __device__ __forceinline__ void launder(u128& v) { asm volatile("" : "+l"(v.lo), "+l"(v.hi)); }
 
-// ---- named barriers (bar.sync / bar.arrive id, count): the persistent kernel
-// splits its CTA into worker warps and look-back warps that meet only at the
-// hand-over points, so the CTA-wide barrier 0 cannot be used inside the tile loop
-template <int ID, int COUNT>
-__device__ __forceinline__ void bar_sync() {
-    asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(COUNT) : "memory");
-}
-template <int ID, int COUNT>
-__device__ __forceinline__ void bar_arrive() {
-    asm volatile("bar.arrive %0, %1;" ::"n"(ID), "n"(COUNT) : "memory");
-}
-template <int ID, int COUNT>
-__device__ __forceinline__ bool bar_red_or(bool p) {
-    int r;
-    asm volatile(
-        "{\n"
-        ".reg .pred p, q;\n"
-        "setp.ne.s32 p, %1, 0;\n"
-        "bar.red.or.pred q, %2, %3, p;\n"
-        "selp.s32 %0, 1, 0, q;\n"
-        "}\n" : "=r"(r) : "r"((int)p), "n"(ID), "n"(COUNT) : "memory");
-    return r != 0;
-}
-constexpr int BAR_WORKERS = 1;   // worker warps only
-constexpr int BAR_CNT = 2;       // workers arrive: sh.cnt + the published partial are ready; look-back warps wait
-constexpr int BAR_EXCL = 3;      // workers arrive: sh.excl is ready; look-back warps wait
-constexpr int BAR_GPTR = 4;      // look-back warps arrive: sh.gptr is ready; workers wait
-
-// barrier among the threads that rank keys: the whole CTA when the look-back is
-// done in line (LBT == 0), the worker warps otherwise
-template <int WORKERS, int LBT>
-__device__ __forceinline__ void workers_sync() {
-    if constexpr (LBT == 0) __syncthreads();
-    else bar_sync<BAR_WORKERS, WORKERS>();
-}
-template <int WORKERS, int LBT>
-__device__ __forceinline__ bool workers_sync_or(bool p) {
-    if constexpr (LBT == 0) return __syncthreads_or(p) != 0;
-    else return bar_red_or<BAR_WORKERS, WORKERS>(p);
-}
-
 // Decoupled look-back for one digit, LB_BATCH predecessors per round trip.
 // p points at the status word of tile `pos` (the nearest predecessor) for this
 // digit; tiles below 0 read as {INCLUSIVE, 0}.
@@ -434,12 +389,37 @@ struct LookBack {
     }
 };
 
-// coalesced run write-out of the digit-sorted tile; VERIFY adds the order check
+// value of lane `src` of the warp, for every element width
+__device__ __forceinline__ unsigned char shfl_elem(unsigned char v, int src) { return (unsigned char)__shfl_sync(FULL_MASK, (unsigned)v, src); }
+__device__ __forceinline__ unsigned short shfl_elem(unsigned short v, int src) { return (unsigned short)__shfl_sync(FULL_MASK, (unsigned)v, src); }
+__device__ __forceinline__ unsigned int shfl_elem(unsigned int v, int src) { return __shfl_sync(FULL_MASK, v, src); }
+__device__ __forceinline__ unsigned long long shfl_elem(unsigned long long v, int src) { return __shfl_sync(FULL_MASK, v, src); }
+__device__ __forceinline__ u128 shfl_elem(u128 v, int src) {
+    u128 r;
+    r.lo = __shfl_sync(FULL_MASK, v.lo, src);
+    r.hi = __shfl_sync(FULL_MASK, v.hi, src);
+    return r;
+}
+
+// Coalesced run write-out of the digit-sorted tile; VERIFY adds the order check
+// (every key against its successor in the tile).  Two slot-to-thread mappings,
+// chosen by element width from what B200 measured (profiles/r01_sweep_v19*):
+//   * elements of 8 bytes and more: warp w owns slots [w*32*ITEMS, (w+1)*32*ITEMS),
+//     row j of it = 32 consecutive slots, one per lane.  The successor of a key
+//     sits in the next lane's register, so it comes by shuffle instead of a second
+//     shared-memory load (2 wavefronts for a 64-bit LDS): lane 0 contributes its
+//     NEXT row's key (what lane 31 needs), the other lanes their own, and lane l
+//     reads from lane l+1 mod 32.  u64 passes 1.164 -> 1.144 ms at 2^28 keys.
+//   * narrower elements: thread t handles slots t, t+THREADS, ...; the successor is
+//     one more 1-wavefront load -- a shuffle is dearer than that (u32 0.756 vs 0.770).
+// (32-bit element offsets instead of the 64-bit addresses in sh.gptr were tried:
+// one wavefront less per warp instruction, but no gain -- v19.)
 template <typename Tr, int THREADS, int ITEMS, bool FULL, bool VERIFY>
 __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& sh, const PassArgs<Tr>& a,
                                           uint32_t xf_out, uint32_t tile_n, int tid) {
     using E = typename Tr::elem_t;
     bool bad = false;
+    const uint32_t n_valid = FULL ? (uint32_t)(THREADS * ITEMS) : tile_n;
     if constexpr (Tr::FEW_BUCKETS) {
         // long runs, expensive digit: copy run by run, no digit per key
         const int buckets = a.prm.nsplit + 1;
@@ -449,18 +429,46 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
             for (uint32_t idx = lo + tid; idx < hi; idx += THREADS)
                 *reinterpret_cast<E*>(base + (unsigned long long)idx * sizeof(E)) = sh.tile[idx];
         }
-        return false;
-    }
+    } else if constexpr (sizeof(E) >= 8) {
+        const int lane = tid & 31;
+        const uint32_t wb = (uint32_t)(tid >> 5) * 32u * ITEMS + (uint32_t)lane;
+        // rolling window of two rows: the compiler hoists as many of the (independent)
+        // loads as it has registers for -- all of them in the one-tile kernel, few in the
+        // streaming kernel, whose key registers already hold the next tile
+        E cur{};
+        if (FULL || wb < n_valid) cur = sh.tile[wb];
 #pragma unroll
-    for (int j = 0; j < ITEMS; ++j) {
-        const uint32_t idx = (uint32_t)j * THREADS + tid;
-        if (FULL || idx < tile_n) {
-            E v = sh.tile[idx];
-            if (VERIFY && (idx + 1 < (FULL ? (uint32_t)(THREADS * ITEMS) : tile_n)))
-                bad |= Tr::prefix_less(sh.tile[idx + 1], v, a.pass, a.prm);
-            const unsigned d = Tr::digit(v, a.pass, a.prm);
-            if (xf_out) v = Tr::xform_out(v, a.prm);
-            *reinterpret_cast<E*>(sh.gptr[d] + (unsigned long long)idx * sizeof(E)) = v;
+        for (int j = 0; j < ITEMS; ++j) {
+            const uint32_t idx = wb + j * 32;
+            E below{};  // the key one row down; past the last row: the next warp's first key (lane 0 only)
+            if (j + 1 < ITEMS) {
+                if (FULL || idx + 32 < n_valid) below = sh.tile[idx + 32];
+            } else if (VERIFY) {
+                if (lane == 0 && idx + 32 < n_valid) below = sh.tile[idx + 32];
+            }
+            E key = cur;
+            if constexpr (VERIFY) {
+                const E nxt = shfl_elem(lane == 0 ? below : key, (lane + 1) & 31);
+                if (idx + 1 < n_valid) bad |= Tr::prefix_less(nxt, key, a.pass, a.prm);
+            }
+            if (FULL || idx < n_valid) {
+                const unsigned d = Tr::digit(key, a.pass, a.prm);
+                if (xf_out) key = Tr::xform_out(key, a.prm);
+                *reinterpret_cast<E*>(sh.gptr[d] + (unsigned long long)idx * sizeof(E)) = key;
+            }
+            cur = below;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) {
+            const uint32_t idx = (uint32_t)j * THREADS + tid;
+            if (FULL || idx < n_valid) {
+                E key = sh.tile[idx];
+                if (VERIFY && idx + 1 < n_valid) bad |= Tr::prefix_less(sh.tile[idx + 1], key, a.pass, a.prm);
+                const unsigned d = Tr::digit(key, a.pass, a.prm);
+                if (xf_out) key = Tr::xform_out(key, a.prm);
+                *reinterpret_cast<E*>(sh.gptr[d] + (unsigned long long)idx * sizeof(E)) = key;
+            }
         }
     }
     return bad;
@@ -469,7 +477,7 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
 // Slow path, out of line: rebuild the tile with ballot ranks (lane-ordered by
 // construction) from the keys still in global memory, and rewrite its slots.
 // Entered by a whole CTA; warp_hist may hold anything; excl/gptr are valid.
-template <typename Tr, int THREADS, int ITEMS, int LBT>
+template <typename Tr, int THREADS, int ITEMS>
 __device__ __noinline__ void rerank_tile(const PassShared<Tr, THREADS, ITEMS> sh,
                                          const PassArgs<Tr>* ap, const typename Tr::elem_t* src_tile,
                                          uint32_t tile_n, uint32_t xf_in, uint32_t xf_out) {
@@ -480,9 +488,9 @@ __device__ __noinline__ void rerank_tile(const PassShared<Tr, THREADS, ITEMS> sh
     const unsigned lane_lt = (1u << lane) - 1u;
     const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
     uint32_t* my_hist = sh.warp_hist + warp * RADIX;
-    workers_sync<THREADS, LBT>();
+    __syncthreads();
     for (int i = tid; i < WARPS * RADIX; i += THREADS) sh.warp_hist[i] = 0;
-    workers_sync<THREADS, LBT>();
+    __syncthreads();
     E e[ITEMS];
     uint32_t rank[ITEMS];
 #pragma unroll
@@ -494,15 +502,15 @@ __device__ __noinline__ void rerank_tile(const PassShared<Tr, THREADS, ITEMS> sh
         }
         rank[i] = ballot_rank<false>(Tr::digit(e[i], a.pass, a.prm), valid, my_hist, lane, lane_lt);
     }
-    workers_sync<THREADS, LBT>();
+    __syncthreads();
     if (tid < RADIX) column_bases<WARPS>(sh.warp_hist, tid, sh.excl[tid]);
-    workers_sync<THREADS, LBT>();
+    __syncthreads();
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i)
         if (wbase + i * 32 < tile_n) sh.tile[rank[i] + my_hist[hidx(Tr::digit(e[i], a.pass, a.prm))]] = e[i];
-    workers_sync<THREADS, LBT>();
+    __syncthreads();
     write_out<Tr, THREADS, ITEMS, false, false>(sh, a, xf_out, tile_n, tid);
-    workers_sync<THREADS, LBT>();
+    __syncthreads();
 }
 
 // One tile whose keys are already in registers (warp-striped: item i of lane l =
@@ -513,10 +521,8 @@ __device__ __noinline__ void rerank_tile(const PassShared<Tr, THREADS, ITEMS> sh
 // Returns true when the order check of the write-out failed (caller re-ranks).
 struct NoHook { __device__ __forceinline__ void operator()() const {} };
 
-// WORKERS threads rank the tile.  LBT == 0: the last 256 of them also run the
-// look-back, in line.  LBT > 0: LBT extra threads (the look-back warps of the
-// persistent kernel) run it concurrently and hand sh.gptr over at BAR_GPTR.
-template <typename Tr, int WORKERS, int ITEMS, bool FULL, int LBT, int LBB, int ABL = 0, typename Hook = NoHook,
+// WORKERS threads rank the tile; the last 256 of them also run the look-back.
+template <typename Tr, int WORKERS, int ITEMS, bool FULL, int LBB, int ABL = 0, typename Hook = NoHook,
           typename Hook2 = NoHook>
 __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, ITEMS>& sh, const PassArgs<Tr>& a,
                                                  const PassPlan& pp, typename Tr::elem_t (&e)[ITEMS],
@@ -557,12 +563,12 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
         for (int i = 0; i < ITEMS; ++i)
             if (FULL || wbase + i * 32 < tile_n) atomicAdd(&my_hist[hidx(Tr::digit(e[i], pass, a.prm))], 1u);
     }
-    workers_sync<WORKERS, LBT>();
+    __syncthreads();
     if constexpr (!Tr::NEEDS_STABLE && !Tr::FEW_BUCKETS) {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) launder(e[i]);
     }
-    after_count();  // persistent kernel: thread 0 starts the bulk copy of the next tile
+    after_count();  // streaming kernel: thread 0 parks the next ticket
 
     // ---- decoupled look-back in line, one digit per thread of the last 256 threads,
     // run AFTER the scatter.  (Requesting the first batch here and resolving it
@@ -605,7 +611,6 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
         // tile's -- and if it ever were, any digit is a correct choice, only slower
         if (count * 2 > tile_n) sh.misc[10] = ((tile + 1u) << 12) | ((uint32_t)(pass & 15) << 8) | (uint32_t)tid;
     }
-    if constexpr (LBT > 0) bar_arrive<BAR_CNT, WORKERS + LBT>();  // the look-back warps start now
     uint32_t incl = count;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -615,7 +620,7 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     // (bits 16+: how many of this warp's 32 digits occur in the tile at all)
     const unsigned occupied = __ballot_sync(FULL_MASK, count != 0);
     if (lane == 31 && warp < RADIX / 32) sh.misc[2 + warp] = incl | ((uint32_t)__popc(occupied) << 16);
-    workers_sync<WORKERS, LBT>();
+    __syncthreads();
     if (tid < RADIX) {
         uint32_t base = 0;
 #pragma unroll
@@ -624,8 +629,7 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
         sh.excl[tid] = excl;
         column_bases<WARPS>(sh.warp_hist, tid, excl);
     }
-    if constexpr (LBT > 0) bar_arrive<BAR_EXCL, WORKERS + LBT>();
-    workers_sync<WORKERS, LBT>();
+    __syncthreads();
 
     // ---- 3. scatter: the returned counter value IS the key's slot in the tile.
     // A returning shared atomic serialises lanes that hit the SAME counter (25 cycles
@@ -694,12 +698,8 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     }
     after_scatter();  // e[] is dead from here on: the streaming kernel re-fills it with the next tile
 
-    if constexpr (LBT == 0) {
-        lookback_inline();
-        __syncthreads();
-    } else {
-        bar_sync<BAR_GPTR, WORKERS + LBT>();  // scatter done by all workers + sh.gptr published
-    }
+    lookback_inline();
+    __syncthreads();
 
     // ---- coalesced run write-out; key-only passes check the order of the tile
     if (ABL & 4) return false;
@@ -708,78 +708,6 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
         return false;
     }
     return write_out<Tr, WORKERS, ITEMS, FULL, true>(sh, a, pp.xf_out, tile_n, tid);
-}
-
-// The look-back warps of the persistent kernel: LBT threads, 256 / LBT digits
-// each, for one tile.  They start as soon as the tile's counts are published --
-// long before the workers need the result -- so the round trips to L2 overlap
-// the scan and the scatter, and the tile's INCLUSIVE words appear early, which
-// keeps every later tile's walk short.
-template <typename Tr, int WORKERS, int ITEMS, int LBT>
-__device__ __forceinline__ void lookback_role(const PassShared<Tr, WORKERS, ITEMS>& sh, const PassArgs<Tr>& a,
-                                              typename Tr::elem_t* dst, uint32_t tile,
-                                              const unsigned long long (&bin)[RADIX / LBT]) {
-    using E = typename Tr::elem_t;
-    constexpr int NDL = RADIX / LBT;
-    const int ltid = (int)threadIdx.x - WORKERS;
-    uint32_t* lb = a.lookback + (size_t)tile * RADIX;
-    bar_sync<BAR_CNT, WORKERS + LBT>();
-    // All NDL digits of a thread walk back together: every round trip to L2 asks
-    // for the next LB_BATCH predecessors of every digit that is still open.  A
-    // batch that contains a word not yet published is asked for again as a whole
-    // (never word by word: serial re-polls multiply the latency, and the depth of
-    // everybody's walk grows with that latency).
-    uint32_t sum[NDL];
-    int pos[NDL];  // nearest predecessor not yet summed; < 0: closed
-#pragma unroll
-    for (int q = 0; q < NDL; ++q) { sum[q] = 0; pos[q] = (int)tile - 1; }
-    const uint32_t* col = a.lookback + ltid;  // status word of tile 0, digit ltid
-    for (;;) {
-        bool any = false;
-#pragma unroll
-        for (int q = 0; q < NDL; ++q) any |= pos[q] >= 0;
-        if (!any) break;
-        uint32_t v[NDL][LB_BATCH];
-#pragma unroll
-        for (int q = 0; q < NDL; ++q)
-#pragma unroll
-            for (int j = 0; j < LB_BATCH; ++j)
-                v[q][j] = (pos[q] - j >= 0) ? ld_relaxed_u32(col + q * LBT + (size_t)(pos[q] - j) * RADIX) : LB_FLAG_INCLUSIVE;
-#pragma unroll
-        for (int q = 0; q < NDL; ++q) {
-            if (pos[q] < 0) continue;
-            uint32_t part = 0;
-            int state = 0;  // 0 walking, 1 reached an inclusive prefix, 2 met an unpublished word
-#pragma unroll
-            for (int j = 0; j < LB_BATCH; ++j) {
-                const uint32_t x = v[q][j];
-                if (state == 0) {
-                    if ((x & (LB_FLAG_PARTIAL | LB_FLAG_INCLUSIVE)) == 0) state = 2;
-                    else {
-                        part += x & LB_VALUE_MASK;
-                        if (x & LB_FLAG_INCLUSIVE) state = 1;
-                    }
-                }
-            }
-            if (state == 2) continue;  // ask for the same batch again
-            sum[q] += part;
-            if (state == 1) {
-                pos[q] = -1;
-                st_relaxed_u32(lb + q * LBT + ltid, LB_FLAG_INCLUSIVE | (sum[q] + sh.cnt[q * LBT + ltid]));
-            } else {
-                pos[q] -= LB_BATCH;
-            }
-        }
-    }
-    bar_sync<BAR_EXCL, WORKERS + LBT>();
-#pragma unroll
-    for (int q = 0; q < NDL; ++q) {
-        const int d = q * LBT + ltid;
-        const unsigned long long gbase = bin[q] + sum[q];
-        sh.gptr[d] = Tr::dst_base((unsigned)d, dst, a.prm) + (gbase - sh.excl[d]) * sizeof(E);
-        if (a.bins_out != nullptr && tile == a.num_tiles - 1) a.bins_out[d] = gbase + sh.cnt[d];
-    }
-    bar_arrive<BAR_GPTR, WORKERS + LBT>();
 }
 
 template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS, int LBB = LB_BATCH, int ABL = 0>
@@ -822,144 +750,17 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     if (tile_n == (uint32_t)TILE) {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) e[i] = ld_elem(src_tile + wbase + i * 32);
-        bad = rank_and_scatter<Tr, THREADS, ITEMS, true, 0, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
+        bad = rank_and_scatter<Tr, THREADS, ITEMS, true, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
     } else {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
             if (wbase + i * 32 < tile_n) e[i] = ld_elem(src_tile + wbase + i * 32);
-        bad = rank_and_scatter<Tr, THREADS, ITEMS, false, 0, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
+        bad = rank_and_scatter<Tr, THREADS, ITEMS, false, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
     }
-    if (Tr::NEEDS_STABLE || a.pass == 0 || (ABL & 31) != 0) return;
+    if (Tr::NEEDS_STABLE || a.pass == 0 || (ABL & 31) != 0) return;  // (bits 0..4 are timing ablations: results wrong on purpose)
     if (!__syncthreads_or(bad)) return;
     if (tid == 0) atomicAdd(a.stats, 1u);
-    rerank_tile<Tr, THREADS, ITEMS, 0>(sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
-}
-
-// ---- TMA bulk copy + mbarrier (sm_90+ PTX; SASS: UBLKCP / SYNCS) ------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "B200_WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra B200_DONE_%=;\n"
-        "bra B200_WAIT_%=;\n"
-        "B200_DONE_%=:\n"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src_gmem, uint32_t bytes, unsigned long long* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-
-template <typename Tr, int WORKERS, int ITEMS, int LBT, int MIN_BLOCKS>
-__global__ void __launch_bounds__(WORKERS + LBT, MIN_BLOCKS)
-onesweep_persistent_kernel(const __grid_constant__ PassArgs<Tr> a) {
-    using E = typename Tr::elem_t;
-    using SM = PassSmem<Tr, WORKERS, ITEMS>;
-    constexpr int WARPS = WORKERS / 32;
-    constexpr int TILE = WORKERS * ITEMS;
-    constexpr uint32_t TILE_BYTES = (uint32_t)SM::TILE_BYTES;
-    static_assert(WORKERS >= RADIX && WORKERS % 32 == 0, "one worker thread per digit needed");
-    static_assert(LBT >= 32 && LBT % 32 == 0 && RADIX % LBT == 0, "look-back warps own 256 / LBT digits per thread");
-    static_assert(TILE_BYTES % 16 == 0, "TMA bulk copies move multiples of 16 bytes");
-
-    const PassPlan pp = a.plan->pass[a.pass];
-    if (pp.skip) return;
-
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    PassShared<Tr, WORKERS, ITEMS> sh(smem_raw, 2 * SM::TILE_BYTES);
-    E* const ring = reinterpret_cast<E*>(smem_raw);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;
-
-    const E* __restrict__ src = (pp.src_is_tmp ? a.tmp : a.keys) + a.portion_off;
-    E* __restrict__ dst = pp.src_is_tmp ? a.keys : a.tmp;
-    const uint32_t full_tiles = a.portion_n / (uint32_t)TILE;  // tiles 0..full_tiles-1 are whole
-
-    // thread 0 is the producer: it draws tickets and starts the bulk copies.  A
-    // CTA holds at most two tickets: the tile it is ranking and the next one, drawn
-    // one tile-time later, so the tiles in flight stay a dense window of the lowest
-    // unfinished ids (a tile's look-back spins on the tile just before it).
-    auto fetch = [&](int slot, uint32_t t) {
-        sh.misc[slot] = t;
-        if (t < full_tiles) {
-            mbar_expect_tx(&sh.mbar[slot], TILE_BYTES);
-            bulk_load(ring + (size_t)slot * TILE, src + (size_t)t * TILE, TILE_BYTES, &sh.mbar[slot]);
-        }
-    };
-    if (tid == 0) {
-        mbar_init(&sh.mbar[0], 1);
-        mbar_init(&sh.mbar[1], 1);
-        fence_mbar_init();
-        fetch(0, atomicAdd(a.ticket, 1u));
-    }
-    for (int i = tid; i < WARPS * RADIX; i += WORKERS + LBT) sh.warp_hist[i] = 0;
-    __syncthreads();
-
-    if (tid >= WORKERS) {
-        // ---- look-back warps: one look-back per tile, concurrent with the workers
-        constexpr int NDL = RADIX / LBT;
-        unsigned long long bin[NDL];
-#pragma unroll
-        for (int q = 0; q < NDL; ++q) bin[q] = a.bins_in[q * LBT + (tid - WORKERS)];
-        for (uint32_t it = 0;; ++it) {
-            const uint32_t tile = sh.misc[it & 1u];
-            if (tile >= a.num_tiles) break;
-            lookback_role<Tr, WORKERS, ITEMS, LBT>(sh, a, dst, tile, bin);
-        }
-        return;
-    }
-
-    for (uint32_t it = 0;; ++it) {
-        const int slot = (int)(it & 1u);
-        const uint32_t tile = sh.misc[slot];
-        if (tile >= a.num_tiles) break;
-        // ticket of the tile that goes into the other slot: asked for now, used
-        // after the count phase, when the atomic has long returned
-        uint32_t next = 0;
-        if (tid == 0) next = atomicAdd(a.ticket, 1u);
-        auto prefetch = [&]() {
-            if (tid == 0) fetch(slot ^ 1, next);
-        };
-        sh.tile = ring + (size_t)slot * TILE;
-        const E* src_tile = src + (size_t)tile * TILE;
-        E e[ITEMS];
-        bool bad;
-        uint32_t tile_n = (uint32_t)TILE;
-        if (tile < full_tiles) {
-            mbar_wait(&sh.mbar[slot], (it >> 1) & 1u);
-#pragma unroll
-            for (int i = 0; i < ITEMS; ++i) e[i] = sh.tile[wbase + i * 32];
-            bad = rank_and_scatter<Tr, WORKERS, ITEMS, true, LBT, LB_BATCH>(sh, a, pp, e, dst, tile, tile_n, prefetch);
-        } else {  // the ragged last tile of the portion: plain guarded loads
-            tile_n = a.portion_n - tile * (uint32_t)TILE;
-#pragma unroll
-            for (int i = 0; i < ITEMS; ++i)
-                if (wbase + i * 32 < tile_n) e[i] = ld_elem(src_tile + wbase + i * 32);
-            bad = rank_and_scatter<Tr, WORKERS, ITEMS, false, LBT, LB_BATCH>(sh, a, pp, e, dst, tile, tile_n, prefetch);
-        }
-        // counters are free once the scatter is over (BAR_GPTR inside rank_and_scatter)
-#pragma unroll
-        for (int i = tid; i < WARPS * RADIX; i += WORKERS) sh.warp_hist[i] = 0;
-        fence_proxy_async();  // generic-proxy accesses of this slot before the next bulk copy into it
-        if (workers_sync_or<WORKERS, LBT>(bad)) {
-            if (tid == 0) atomicAdd(a.stats, 1u);
-            rerank_tile<Tr, WORKERS, ITEMS, LBT>(sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
-            for (int i = tid; i < WARPS * RADIX; i += WORKERS) sh.warp_hist[i] = 0;
-            fence_proxy_async();
-            workers_sync<WORKERS, LBT>();
-        }
-    }
+    rerank_tile<Tr, THREADS, ITEMS>(sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
 }
 
 // ---------------------------------------------------------------------------

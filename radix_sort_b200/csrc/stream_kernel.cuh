@@ -88,16 +88,16 @@ onesweep_stream_kernel(const __grid_constant__ PassArgs<Tr> a) {
         const uint32_t tile_n = min((uint32_t)TILE, a.portion_n - tile * (uint32_t)TILE);
         bool bad;
         if (tile_n == (uint32_t)TILE)
-            bad = rank_and_scatter<Tr, THREADS, ITEMS, true, 0, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, park_ticket, prefetch);
+            bad = rank_and_scatter<Tr, THREADS, ITEMS, true, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, park_ticket, prefetch);
         else
-            bad = rank_and_scatter<Tr, THREADS, ITEMS, false, 0, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, park_ticket, prefetch);
+            bad = rank_and_scatter<Tr, THREADS, ITEMS, false, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, park_ticket, prefetch);
         // end-of-tile barrier: the write-out has read sh.tile / sh.gptr before the
         // next tile's phases overwrite them
         if (Tr::NEEDS_STABLE || a.pass == 0) {
             __syncthreads();
         } else if (__syncthreads_or(bad)) {
             if (tid == 0) atomicAdd(a.stats, 1u);
-            rerank_tile<Tr, THREADS, ITEMS, 0>(sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
+            rerank_tile<Tr, THREADS, ITEMS>(sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
 #pragma unroll
             for (int i = lane; i < RADIX; i += 32) my_hist[i] = 0;
             __syncthreads();

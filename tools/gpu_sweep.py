@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--param", type=float, default=0.0)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--flags", type=int, default=0)  # b200sort flags (FLAG_NO_SKIP)
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     peak = 6552.0
@@ -42,7 +43,7 @@ def main():
                 for r in range(a.reps + 1):
                     keys.copy_(src)
                     torch.cuda.synchronize()
-                    t = rs.sort_timed(keys, k, workspace=ws)
+                    t = rs.sort_timed(keys, k, workspace=ws, flags=a.flags)
                     if r == 0:
                         continue  # warm-up
                     if best is None or t["total_ms"] < best["total_ms"]:
@@ -53,7 +54,7 @@ def main():
                 passes = [p for p in best["pass_ms"] if p > 0.002]
                 pass_ms = sum(passes) / max(1, len(passes))
                 out = {
-                    "kind": kname, "n": n, "variant": v, "distr": a.distr, "ok": ok,
+                    "kind": kname, "n": n, "variant": v, "distr": a.distr, "flags": a.flags, "ok": ok,
                     "total_ms": round(best["total_ms"], 4), "hist_ms": round(best["hist_ms"], 4),
                     "scan_ms": round(best["scan_ms"], 4), "copy_back_ms": round(best["copy_back_ms"], 4),
                     "pass_ms": [round(p, 4) for p in best["pass_ms"]],
