@@ -157,8 +157,8 @@ int sort_front(const SortCall& c) {
         B200_CU(cudaMemcpyAsync(bins, c.peer_offsets, (size_t)(c.nsplit + 1) * 8, cudaMemcpyDeviceToDevice, st));
 
     // K3: one launch per digit per portion
-    size_t lb_cursor = 0;
     for (int p = 0; p < D; ++p) {
+        size_t lb_cursor = 0;  // tiles of the portions before q: every pass lays its portions out alike
         for (int q = 0; q < L.portions; ++q) {
             const size_t off = (size_t)q * L.portion_elems;
             const size_t pn = (q + 1 < L.portions) ? L.portion_elems : n - off;
@@ -174,6 +174,7 @@ int sort_front(const SortCall& c) {
             a.bins_in = bins + ((size_t)p * L.portions + q) * RADIX;
             a.bins_out = (q + 1 < L.portions) ? bins + ((size_t)p * L.portions + q + 1) * RADIX : nullptr;
             a.lookback = lookback + lb_cursor * RADIX;
+            a.lookback_half = (FAM == FAM_PARTITION) ? 0 : L.tiles_total * RADIX;
             a.ticket = tickets + (size_t)p * L.portions + q;
             a.stats = stats;
             a.prm = prm;

@@ -60,8 +60,8 @@ template <int FAM, int W> struct Variants;
 template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}, {3, 512, 32, 2, 0}}; };
 #define B200_NV_KEYS_2 2
 template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}, {3, 512, 24, 2, 0}}; };
-#define B200_NV_KEYS_4 3
-template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 22, 2, 0}, {3, 512, 22, 2, 0}, {0, 512, 16, 2, 0}}; };
+#define B200_NV_KEYS_4 4
+template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 26, 2, 0}, {3, 512, 22, 2, 0}, {0, 512, 22, 2, 0}, {0, 512, 16, 2, 0}}; };
 #define B200_NV_KEYS_8 3
 template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {3, 512, 16, 2, 0}, {0, 256, 20, 3, 0}}; };
 #define B200_NV_KEYS_16 2
@@ -166,7 +166,7 @@ inline Layout make_layout(size_t n, size_t elem_bytes, int digits, int tile, boo
     L.hist_off = off;   off = align_up(off + (size_t)digits * RADIX * 8, 256);
     L.ticket_off = off; off = align_up(off + (size_t)digits * L.portions * 4, 256);
     L.stats_off = off;  off += 256;
-    L.lb_off = off;     off = align_up(off + (size_t)digits * L.tiles_total * RADIX * 4, 256);
+    L.lb_off = off;     off = align_up(off + (size_t)(with_tmp ? 2 : 1) * L.tiles_total * RADIX * 4, 256);  // two halves, swapped per executed pass
     L.total = off;
     L.zero_off = L.hist_off;
     L.zero_bytes = L.total - L.hist_off;

@@ -252,7 +252,10 @@ struct PassArgs {
     uint32_t grid;                       // CTAs to launch (streaming kernel: resident CTAs)
     const unsigned long long* bins_in;   // [256] global base of each bucket for this portion
     unsigned long long* bins_out;        // [256] base for the next portion (or null)
-    uint32_t* lookback;                  // [num_tiles][256] status words, zeroed
+    uint32_t* lookback;                  // [2][num_tiles][256] status words, zeroed.  An executed pass uses half
+                                         // plan.src_is_tmp (the parity of the passes executed before it) and
+                                         // zeroes the other half for the next executed pass
+    size_t lookback_half;                // words between the halves; 0 = one half only (single-pass partition)
     uint32_t* ticket;                    // tile-id dispenser, zeroed
     uint32_t* stats;                     // [0] tiles that took the re-rank fallback
     typename Tr::Params prm;
@@ -575,7 +578,7 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     // before the scatter publishes INCLUSIVE words sooner, but the walk then meets
     // predecessors that have not even published their counts and spins: 5-30 %
     // slower, profiles/r01_sweep_v12_early_lookback.jsonl.)
-    uint32_t* lb = a.lookback + (size_t)tile * RADIX;
+    uint32_t* lb = a.lookback + (pp.src_is_tmp ? a.lookback_half : 0) + (size_t)tile * RADIX;
     auto lookback_inline = [&]() {
         if (tid >= LB0) {
             const int d = tid - LB0;
@@ -604,6 +607,8 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     if (tid < RADIX) {
         count = column_total<WARPS>(sh.warp_hist, tid);
         st_relaxed_u32(lb + tid, (tile == 0 ? LB_FLAG_INCLUSIVE : LB_FLAG_PARTIAL) | count);
+        // the same tile's words in the other half: nobody reads them before the next launch
+        if (a.lookback_half) a.lookback[(pp.src_is_tmp ? 0 : a.lookback_half) + (size_t)tile * RADIX + tid] = 0u;
         sh.cnt[tid] = count;
         // a digit that holds more than half of the tile (at most one can) is ranked
         // without atomics in the scatter; the word is tagged with tile id and pass so

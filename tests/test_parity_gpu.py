@@ -88,7 +88,10 @@ def test_ref_tuple(cuda):  # tests.rs:175-187: random (u32,u32), stable sort_by_
 
 # ---- every kind, device-resident path, edge sizes ----------------------------------
 
-EDGE_SIZES = [1, 2, 31, 32, 33, 95, 96, 97, 255, 256, 257, 3071, 3072, 3073, 8191, 8192, 8193, 16385, 100_003]
+# tile sizes of the shipped K3 variants (csrc/sort_impl.cuh): 3072 (16-byte), 6144 (8-byte records),
+# 8192 (8-byte keys), 12288 (2-byte), 13312 (4-byte), 16384 (1-byte)
+EDGE_SIZES = [1, 2, 31, 32, 33, 95, 96, 97, 255, 256, 257, 3071, 3072, 3073, 6143, 6144, 6145, 8191, 8192, 8193,
+              12287, 12288, 12289, 13311, 13312, 13313, 16383, 16384, 16385, 26625, 100_003]
 
 
 @pytest.mark.parametrize("kind", _ref.KINDS)
