@@ -69,18 +69,23 @@ __device__ __forceinline__ u128 ld_elem<u128>(const u128* p) {
 // is not slowed by same-address lanes (the unit merges them), so skewed inputs
 // need no software warp aggregation -- the ballot/branch version of this kernel
 // spent 68 instructions per 32 keys for 21 % of HBM peak.  What does cost is bank
-// conflicts between DIFFERENT digits: with 8 copies per bin the kernel ran the
-// SM's LSU data pipe at 96 % (ncu, 3.0 wavefronts per atomic) for 2.6 TB/s.  So
-// every bin has R copies, the copy chosen by lane % R, with R as large as 128 KB
-// of shared memory allows: R = 32 (keys of <= 4 bytes) puts lane l on bank l for
-// every digit -- one wavefront per atomic, no conflicts at all; R = 16 (8-byte
-// keys) leaves one possible partner lane, R = 8 (16-byte keys) three.
+// conflicts between DIFFERENT digits, so every bin has R copies, the copy chosen
+// by lane % R, with R as large as 128 KB of shared memory allows: R = 32 (keys of
+// <= 4 digits) puts lane l on bank l for every digit -- one wavefront per atomic,
+// no conflicts at all; with R = 16 (8-byte keys) lanes l and l+16 collide whenever
+// their digits have the same parity -- two wavefronts per atomic, the LSU data pipe
+// at 95 % of its peak, 3.9 TB/s (profiles/r01_ncu_k1_final_u64_2p27.txt); R = 8 for
+// 16-byte keys.  Tried for 8-byte keys and dropped: two 16-bit counters per word
+// (R = 32 in 16 KB per digit, flushed every 253 rounds) -- conflict-free, but the atomic
+// then adds 1 or 1 << 16, and a generic ATOMS.ADD costs 3.3 cycles per warp instruction
+// where the +1 form (ATOMS.POPC.INC) costs 1-2: 2.8 TB/s (r01_sweep_v23).
 // ---------------------------------------------------------------------------
 template <typename Tr>
 struct HistCfg {
+    static constexpr int THREADS = 1024;
     static constexpr int R = Tr::DIGITS <= 4 ? 32 : Tr::DIGITS <= 8 ? 16 : 8;
     static constexpr size_t SMEM = (size_t)Tr::DIGITS * RADIX * R * sizeof(uint32_t);
-    static constexpr int THREADS = 1024;
+    static constexpr int VEC = 16 / (int)sizeof(typename Tr::elem_t);
 };
 
 template <typename Tr, int THREADS>
@@ -90,7 +95,7 @@ hist_all_digits_kernel(const typename Tr::elem_t* __restrict__ in, size_t n,
     using E = typename Tr::elem_t;
     constexpr int D = Tr::DIGITS;
     constexpr int R = HistCfg<Tr>::R;
-    constexpr int VEC = 16 / (int)sizeof(E);
+    constexpr int VEC = HistCfg<Tr>::VEC;
     extern __shared__ __align__(16) uint32_t hist_sh[];
     const int tid = threadIdx.x;
     for (int i = tid; i < D * RADIX * R; i += THREADS) hist_sh[i] = 0;
@@ -117,21 +122,23 @@ hist_all_digits_kernel(const typename Tr::elem_t* __restrict__ in, size_t n,
     const size_t nvec = (n - head) / VEC;
     const size_t tail = head + nvec * VEC;
 
+    // A round = four vectors per thread, `stride` apart; `rounds` = the rounds this thread
+    // has all four of.  Software pipeline: the four vectors of the next round are requested
+    // before the current four are counted, so HBM and the atomic unit work at the same time.
     const size_t stride = (size_t)gridDim.x * THREADS;
     size_t i = (size_t)blockIdx.x * THREADS + tid;
-    // software pipeline: the four vectors of the next round are requested before
-    // the current four are counted, so HBM and the atomic unit work at the same time
-    if (i + 3 * stride < nvec) {
+    const size_t mine_last = i + 3 * stride;  // my last vector of round 0
+    const size_t rounds = nvec > mine_last ? (nvec - 1 - mine_last) / (4 * stride) + 1 : 0;
+    if (rounds) {
         uint4 a = __ldg(vec + i), b = __ldg(vec + i + stride), c = __ldg(vec + i + 2 * stride), d = __ldg(vec + i + 3 * stride);
-        for (;;) {
-            const size_t ni = i + 4 * stride;
-            const bool more = ni + 3 * stride < nvec;
+        for (size_t r = 1;; ++r) {
+            i += 4 * stride;
+            const bool more = r < rounds;
             uint4 na, nb, nc, nd;
             if (more) {
-                na = __ldg(vec + ni); nb = __ldg(vec + ni + stride); nc = __ldg(vec + ni + 2 * stride); nd = __ldg(vec + ni + 3 * stride);
+                na = __ldg(vec + i); nb = __ldg(vec + i + stride); nc = __ldg(vec + i + 2 * stride); nd = __ldg(vec + i + 3 * stride);
             }
             count_vec(a); count_vec(b); count_vec(c); count_vec(d);
-            i = ni;
             if (!more) break;
             a = na; b = nb; c = nc; d = nd;
         }

@@ -466,7 +466,7 @@ def test_partition_count_then_exchange_into_separate_buffers(kind, cuda):
 
 # ---- full-size runs: size-independent properties (sorted + same multiset) ------------
 
-def _property_run(kind, n, dist, param, cuda, seed=0xB2000002):
+def _property_run(kind, n, dist, param, cuda, seed=0xB2000002, flags=0):
     import torch
     k = _kind(kind)
     t = distr.empty_keys(n, k, cuda)
@@ -474,7 +474,7 @@ def _property_run(kind, n, dist, param, cuda, seed=0xB2000002):
     fp = verify.fingerprint(t, k)
     assert fp[0] == n
     ws = torch.empty(rs.temp_bytes(n, k), dtype=torch.uint8, device=cuda)
-    rs.radix_sort(t, k, workspace=ws)
+    rs.radix_sort(t, k, workspace=ws, flags=flags)
     torch.cuda.synchronize()
     assert verify.count_unsorted(t, k) == 0, "not sorted"
     assert verify.fingerprint(t, k) == fp, "multiset changed"
@@ -495,6 +495,14 @@ def test_config3_transform_kinds_properties(kind, dist, param, cuda):  # configs
 @pytest.mark.parametrize("dist,param", [(distr.Distr.ZIPF, 1.0), (distr.Distr.STEP, 16), (distr.Distr.ASCENDING, 2_000_000_000)])
 def test_config4_2b_u32_skew_properties(dist, param, cuda):  # configs[3]: n > 2^30 -> two look-back portions
     _property_run("u32", 2_000_000_000, dist, param, cuda)
+
+
+@pytest.mark.parametrize("kind,n,m", [("u64", 1 << 29, 1), ("i64", 1 << 28, 2), ("u128", 1 << 27, 1), ("u32", 1 << 30, 3)])
+def test_few_values_at_scale_no_skip(kind, n, m, cuda):
+    # m distinct values put every increment of a K1 CTA on m shared-memory counters (32-bit:
+    # they must not wrap below 2^32 / CTAs keys) and every K3 tile on m digits per pass;
+    # NO_SKIP: the passes really run and use the bucket bases.
+    _property_run(kind, n, distr.Distr.STEP, m, cuda, flags=rs.FLAG_NO_SKIP)
 
 
 def test_portion_boundary_small_keys(cuda):
