@@ -581,10 +581,10 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     after_count();  // streaming kernel: thread 0 parks the next ticket
 
     // ---- decoupled look-back in line, one digit per thread of the last 256 threads,
-    // run AFTER the scatter.  (Requesting the first batch here and resolving it
-    // before the scatter publishes INCLUSIVE words sooner, but the walk then meets
-    // predecessors that have not even published their counts and spins: 5-30 %
-    // slower, profiles/r01_sweep_v12_early_lookback.jsonl.)
+    // run AFTER the scatter.  (Walking before the scatter publishes INCLUSIVE words
+    // sooner but meets predecessors that have not published yet: 5-30 % slower with the
+    // branchy walk, profiles/r01_sweep_v12_early_lookback.jsonl; with the branch-free
+    // walk it is a tie, profiles/r01_sweep_v25_early_lookback_again.jsonl.)
     uint32_t* lb = a.lookback + (pp.src_is_tmp ? a.lookback_half : 0) + (size_t)tile * RADIX;
     auto lookback_inline = [&]() {
         if (tid >= LB0) {
