@@ -122,13 +122,16 @@ hist_all_digits_kernel(const typename Tr::elem_t* __restrict__ in, size_t n,
     const size_t nvec = (n - head) / VEC;
     const size_t tail = head + nvec * VEC;
 
-    // A round = four vectors per thread, `stride` apart; `rounds` = the rounds this thread
-    // has all four of.  Software pipeline: the four vectors of the next round are requested
-    // before the current four are counted, so HBM and the atomic unit work at the same time.
+    // A round = four vectors per thread, `stride` apart; `rounds` = the rounds in which EVERY
+    // thread of this CTA has all four (a CTA-uniform trip count: the loop control stays in
+    // uniform registers; u32 K1 0.90 -> 0.82 ms at 1 B keys against a per-thread count); at
+    // most four vectors per thread are left for the strided loop below.  Software pipeline:
+    // the four vectors of the next round are requested before the current four are counted,
+    // so HBM and the atomic unit work at the same time.
     const size_t stride = (size_t)gridDim.x * THREADS;
     size_t i = (size_t)blockIdx.x * THREADS + tid;
-    const size_t mine_last = i + 3 * stride;  // my last vector of round 0
-    const size_t rounds = nvec > mine_last ? (nvec - 1 - mine_last) / (4 * stride) + 1 : 0;
+    const size_t cta_last = (size_t)blockIdx.x * THREADS + (THREADS - 1) + 3 * stride;  // the CTA's last vector of round 0
+    const size_t rounds = nvec > cta_last ? (nvec - 1 - cta_last) / (4 * stride) + 1 : 0;
     if (rounds) {
         uint4 a = __ldg(vec + i), b = __ldg(vec + i + stride), c = __ldg(vec + i + 2 * stride), d = __ldg(vec + i + 3 * stride);
         for (size_t r = 1;; ++r) {
