@@ -211,6 +211,12 @@ def run_gpu(args):
                 exchange_note = f"nccl all_to_all_single (peer memory unavailable: {type(e).__name__}: {str(e)[:120]})"
         if exchange is None:
             sendbuf = torch.empty_like(pristine)
+    # overlapped exchange: ranges cut in two, the second halves cross NVLink while the first are sorted
+    # (measured slower than the one-piece exchange at N = 2 and N = 8 -- profiles/r01_bench_n*_overlap_*.json -- so opt-in)
+    overlap = exchange is not None and args.overlap == "on" and 2 * world <= mgpu.MAX_RANKS
+    ws2 = torch.empty(rs.temp_bytes(int(n * 0.75) + 1024, K), dtype=torch.uint8, device=dev) if overlap else None
+    if overlap:
+        exchange_note += "; exchange in two pieces, the second overlapped with the local sort of the first"
 
     def barrier():
         if dist is not None:
@@ -227,7 +233,8 @@ def run_gpu(args):
             rs.radix_sort(keys, K, workspace=ws)
             out = keys
         else:
-            out = mgpu.sort_sharded(keys, K, workspace=ws, send_buffer=sendbuf, exchange=exchange).keys
+            out = mgpu.sort_sharded(keys, K, workspace=ws, send_buffer=sendbuf, exchange=exchange, overlap=overlap,
+                                    workspace2=ws2).keys
         e1.record()
         torch.cuda.synchronize()
         return e0.elapsed_time(e1), out
@@ -251,7 +258,8 @@ def run_gpu(args):
     if world > 1:  # one extra, untimed step with per-phase device timings
         keys.copy_(pristine)
         barrier()
-        out = mgpu.sort_sharded(keys, K, workspace=ws, send_buffer=sendbuf, exchange=exchange, timings=phases).keys
+        out = mgpu.sort_sharded(keys, K, workspace=ws, send_buffer=sendbuf, exchange=exchange, timings=phases,
+                                overlap=overlap, workspace2=ws2).keys
         barrier()
 
     # correctness of the last timed step: sorted + same multiset <=> bit-identical to the reference's output
@@ -381,7 +389,8 @@ def run_gpu(args):
             _ffi.check(rc)
         else:
             keys.copy_(host[:n], non_blocking=True)
-            res = mgpu.sort_sharded(keys, K, workspace=ws, send_buffer=sendbuf, exchange=exchange)
+            res = mgpu.sort_sharded(keys, K, workspace=ws, send_buffer=sendbuf, exchange=exchange, overlap=overlap,
+                                    workspace2=ws2)
             host[: res.n_out].copy_(res.keys, non_blocking=True)
             torch.cuda.synchronize()
             d2h = res.n_out * KEY_BYTES
@@ -434,6 +443,8 @@ def run_gpu(args):
     xms = phases.get("exchange") or phases.get("all_to_all")
     if world > 1 and xms:
         sent = (world - 1) / world * n * KEY_BYTES
+        if overlap:  # the timed "exchange" phase is the first of the two pieces: half of the bytes
+            sent /= 2
         nvlink = {"sent_bytes_per_gpu": int(sent), "exchange_ms": round(xms, 3), "GBps_per_direction": round(sent / (xms * 1e-3) / 1e9, 1),
                   "frac_of_900": round(sent / (xms * 1e-3) / 1e9 / 900.0, 3)}
     line = {
@@ -483,6 +494,8 @@ def main():
     ap.add_argument("--no-u32", action="store_true", help="skip the secondary u32 measurement")
     ap.add_argument("--no-e2e", action="store_true",
                     help="skip the host-buffer leg (evidence runs at sizes whose pinned host copies would not fit the box)")
+    ap.add_argument("--overlap", default="off", choices=["on", "off"],
+                    help="N > 1, fused exchange: send the buckets in two pieces and sort the first while the second travels")
     ap.add_argument("--exchange", default="auto", choices=["auto", "fused", "nccl"],
                     help="N > 1: fused K7 peer stores, NCCL all-to-all, or fused with fallback (default)")
     args = ap.parse_args()

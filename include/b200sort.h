@@ -197,6 +197,17 @@ int b200sort_partition_count_device(const void *d_in, void *d_tmp, size_t tmp_by
 int b200sort_partition_exchange_device(const void *d_in, void *d_tmp, size_t tmp_bytes, size_t n, int kind,
                                        const void *splitters, int nsplit, void *const *peer_bases,
                                        const uint64_t *d_peer_offsets, void *stream);
+/* Step 3 in pieces, so that the receiver can start sorting the buckets of one
+ * piece while the next piece is still crossing NVLink: stores only the buckets
+ * whose bit is set in bucket_mask (bit r = bucket r); the other keys are read
+ * and ranked but not written.  again = 0 for the first piece after the count
+ * call, 1 for every later piece over the same d_tmp (re-arms the tile tickets
+ * and look-back state the previous piece consumed).  Pieces over one d_tmp must
+ * not overlap in time (enqueue them in stream order). */
+int b200sort_partition_exchange_part_device(const void *d_in, void *d_tmp, size_t tmp_bytes, size_t n, int kind,
+                                            const void *splitters, int nsplit, void *const *peer_bases,
+                                            const uint64_t *d_peer_offsets, unsigned bucket_mask, int again,
+                                            void *stream);
 
 #ifdef __cplusplus
 }

@@ -492,7 +492,8 @@ int b200sort_partition_device(const void* d_in, void* d_out, void* d_tmp, size_t
 
 static int partition_phase(int phase, const void* d_in, void* d_tmp, size_t tmp_bytes, size_t n, int kind,
                            const void* splitters, int nsplit, uint64_t* d_counts, void* const* peer_bases,
-                           const uint64_t* d_peer_offsets, void* stream) {
+                           const uint64_t* d_peer_offsets, void* stream, unsigned bucket_mask = 0xFFFFFFFFu,
+                           bool rezero = false) {
     if (nsplit < 0 || nsplit > MAX_SPLITTERS) return fail(B200SORT_ERR_INVALID_ARG, "nsplit must be in [0, 15]");
     if (nsplit > 0 && !splitters) return fail(B200SORT_ERR_INVALID_ARG, "null splitters");
     if (n && !d_in) return fail(B200SORT_ERR_INVALID_ARG, "null device pointer");
@@ -511,6 +512,7 @@ static int partition_phase(int phase, const void* d_in, void* d_tmp, size_t tmp_
         c.hist_copy = reinterpret_cast<unsigned long long*>(d_counts); c.hist_copy_words = nsplit + 1;
     }
     c.splitters = splitters; c.nsplit = nsplit; c.phase = phase;
+    c.bucket_mask = bucket_mask; c.rezero = rezero;
     c.peer_bases = peer_bases; c.peer_offsets = reinterpret_cast<const unsigned long long*>(d_peer_offsets);
     return front_by_width<FAM_PARTITION>(kb, c);
 }
@@ -526,6 +528,13 @@ int b200sort_partition_exchange_device(const void* d_in, void* d_tmp, size_t tmp
                                        const uint64_t* d_peer_offsets, void* stream) {
     return partition_phase(SortCall::PHASE_SCATTER, d_in, d_tmp, tmp_bytes, n, kind, splitters, nsplit, nullptr,
                            peer_bases, d_peer_offsets, stream);
+}
+
+int b200sort_partition_exchange_part_device(const void* d_in, void* d_tmp, size_t tmp_bytes, size_t n, int kind,
+                                            const void* splitters, int nsplit, void* const* peer_bases,
+                                            const uint64_t* d_peer_offsets, unsigned bucket_mask, int again, void* stream) {
+    return partition_phase(SortCall::PHASE_SCATTER, d_in, d_tmp, tmp_bytes, n, kind, splitters, nsplit, nullptr,
+                           peer_bases, d_peer_offsets, stream, bucket_mask, again != 0);
 }
 
 unsigned long long b200sort_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }

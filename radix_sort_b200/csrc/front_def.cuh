@@ -46,6 +46,7 @@ int make_params(const SortCall& c, typename FamilyTraits<FAM, W>::type::Params* 
         using U = typename Tr::elem_t;
         p.nsplit = c.nsplit;
         p.xf = c.xf;
+        p.mask = c.bucket_mask;
         const U* raw = static_cast<const U*>(c.splitters);
         for (int j = 0; j < c.nsplit; ++j) p.spl[j] = to_ordered_rt<U>(raw[j], c.xf);
         for (int j = c.nsplit; j < MAX_SPLITTERS; ++j) std::memset(&p.spl[j], 0xFF, sizeof(U));  // padding: largest ordered value
@@ -73,7 +74,9 @@ int sort_front(const SortCall& c) {
     typename Tr::Params prm;
     if (int rc = make_params<FAM, W>(c, &prm)) return rc;
     const int ph = c.phase;
-    const bool do_zero = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT || ph == SortCall::PHASE_COUNT_BEGIN;
+    // (a second scatter over the same counts zeroes the same region: the histogram in it is spent by then)
+    const bool do_zero = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT || ph == SortCall::PHASE_COUNT_BEGIN ||
+                         (ph == SortCall::PHASE_SCATTER && c.rezero);
     const bool do_hist = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT || ph == SortCall::PHASE_COUNT_PART;
     const bool do_plan = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT || ph == SortCall::PHASE_COUNT_END;
     const bool do_scatter = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_SCATTER;

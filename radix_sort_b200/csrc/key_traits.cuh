@@ -189,6 +189,9 @@ struct PartitionTraits {
         // this process (peer memory over NVLink); bucket r is then stored there
         // directly and bins_in[r] counts elements from the start of THAT buffer
         unsigned long long peer[MAX_SPLITTERS + 1];
+        // buckets this launch writes out (bit r = bucket r); the others are ranked but not
+        // stored -- the overlapped multi-GPU exchange sends the buckets in two launches
+        unsigned mask;
     };
     __device__ __forceinline__ static bool prefix_less(elem_t, elem_t, int, const Params&) { return false; }
     __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params&) { return e; }

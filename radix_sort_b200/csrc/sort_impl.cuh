@@ -215,6 +215,8 @@ struct SortCall {
     enum { PHASE_ALL = 0, PHASE_COUNT = 1, PHASE_SCATTER = 2, PHASE_COUNT_BEGIN = 3, PHASE_COUNT_PART = 4, PHASE_COUNT_END = 5 };
     int phase = PHASE_ALL;
     size_t part_off = 0, part_n = 0;
+    unsigned bucket_mask = 0xFFFFFFFFu;              // PHASE_SCATTER: buckets this launch stores (bit r = bucket r)
+    bool rezero = false;                             // PHASE_SCATTER run again on the same state: zero tickets + look-back first
     void* const* peer_bases = nullptr;               // host array, nsplit + 1 device pointers
     const unsigned long long* peer_offsets = nullptr;  // device array, nsplit + 1 element offsets
 };

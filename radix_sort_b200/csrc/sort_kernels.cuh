@@ -437,6 +437,7 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
         // long runs, expensive digit: copy run by run, no digit per key
         const int buckets = a.prm.nsplit + 1;
         for (int b = 0; b < buckets; ++b) {
+            if (!((a.prm.mask >> b) & 1u)) continue;
             const uint32_t lo = sh.excl[b], hi = lo + sh.cnt[b];
             const unsigned long long base = sh.gptr[b];
             for (uint32_t idx = lo + tid; idx < hi; idx += THREADS)

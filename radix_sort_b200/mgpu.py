@@ -84,6 +84,22 @@ def send_offsets(count_matrix: np.ndarray, rank: int):
     return [int(x) for x in cm[:rank, :].sum(axis=0)]
 
 
+def halved_plan(count_matrix: np.ndarray, rank: int):
+    """Overlapped exchange: every rank's range is cut in two by one more splitter, so
+    count_matrix[s][j] counts the keys rank s holds of SUB-range j (2 * world of them;
+    sub-ranges 2d and 2d+1 belong to rank d and lie back to back in d's receive
+    buffer, each filled in sender-rank order).  Returns (offsets, first, second):
+    offsets[j] = element offset in rank j//2's receive buffer at which `rank`'s
+    keys of sub-range j start; first[d] / second[d] = keys rank d receives in its
+    first / second sub-range."""
+    cm = np.asarray(count_matrix, dtype=np.int64)
+    tot = cm.sum(axis=0)
+    first, second = tot[0::2], tot[1::2]
+    before = cm[:rank, :].sum(axis=0)
+    offsets = [int(before[j] + (first[j // 2] if j % 2 else 0)) for j in range(cm.shape[1])]
+    return offsets, [int(x) for x in first], [int(x) for x in second]
+
+
 class PeerExchange:
     """Receive buffers of all ranks of `group`, each `capacity_keys` keys, mapped
     into every process (torch symmetric memory: CUDA VMM allocations exchanged
@@ -109,10 +125,11 @@ class PeerExchange:
         self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
         self.recv_rows = self.buf.view(self.capacity, self.key_bytes)
 
-    def barrier(self):
+    def barrier(self, channel: int = 0):
         """Device-side barrier on the current stream: every rank's stores into
-        every receive buffer are complete and visible after it."""
-        self.handle.barrier(channel=0)
+        every receive buffer are complete and visible after it.  Barriers that can
+        be in flight at the same time (on different streams) need different channels."""
+        self.handle.barrier(channel=channel)
 
 
 class CudaOps:
@@ -189,6 +206,38 @@ class CudaOps:
         workspace.record_stream(self.torch.cuda.current_stream(self.device))
         exchange.barrier()
 
+    def partition_exchange_part(self, rows, kind: Kind, splitters_host: np.ndarray, workspace, exchange, offsets,
+                                owners, bucket_mask: int, again: bool, channel: int):
+        """One piece of the K7 scatter phase: only the buckets in `bucket_mask` are stored
+        (bucket j into the receive buffer of rank owners[j]), then a barrier on `channel`."""
+        n = rows.shape[0]
+        nsplit = int(splitters_host.shape[0])
+        spl = np.ascontiguousarray(splitters_host)
+        bases = (ctypes.c_void_p * (nsplit + 1))(*[exchange.peer_ptrs[o] for o in owners])
+        check(self.lib.b200sort_partition_exchange_part_device(rows.data_ptr(), workspace.data_ptr(), workspace.numel(), n,
+                                                               int(kind), spl.ctypes.data if nsplit else None, nsplit, bases,
+                                                               offsets.data_ptr(), int(bucket_mask), 1 if again else 0,
+                                                               self._stream()))
+        workspace.record_stream(self.torch.cuda.current_stream(self.device))
+        exchange.barrier(channel)
+
+    def side_stream(self):
+        """A second stream (created once) for the piece of the exchange that overlaps the first local sort."""
+        if getattr(self, "_side", None) is None:
+            self._side = self.torch.cuda.Stream(self.device)
+        return self._side
+
+    def fork(self, side):
+        """`side` waits for everything enqueued so far on the current stream."""
+        side.wait_stream(self.torch.cuda.current_stream(self.device))
+
+    def on(self, stream):
+        return self.torch.cuda.stream(stream)
+
+    def join(self, side):
+        """The current stream waits for everything enqueued so far on `side`."""
+        self.torch.cuda.current_stream(self.device).wait_stream(side)
+
     def workspace_for(self, n: int, kind: Kind, workspace=None):
         need = temp_bytes(max(n, 1), kind)
         if workspace is None or workspace.numel() < need:
@@ -218,7 +267,8 @@ class ShardedResult:
 
 
 def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 << 14, seed: int = 0xB200,
-                 workspace=None, send_buffer=None, exchange=None, timings: Optional[dict] = None) -> ShardedResult:
+                 workspace=None, send_buffer=None, exchange=None, timings: Optional[dict] = None,
+                 overlap: bool = False, workspace2=None) -> ShardedResult:
     """Sort keys sharded over the ranks of `group`.  `keys`: this rank's shard
     (contiguous CUDA tensor; (n, 2) uint64 for 128-bit kinds).  Collective: every
     rank of the group must call it.  Returns this rank's slice of the sorted order
@@ -228,7 +278,12 @@ def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 
     buffers; the result is a view of this rank's receive buffer).  A sort whose
     largest shard would not fit the exchange's capacity falls back, on all ranks
     together, to the all-to-all path.  timings: dict filled with per-phase
-    milliseconds (device time on the current stream)."""
+    milliseconds (device time on the current stream).
+
+    overlap (fused path, world <= 8): every rank's range is cut in two by one more
+    splitter; the first halves are exchanged, then the second halves cross NVLink on
+    a side stream WHILE every rank already sorts its first half (workspace2: a second
+    sort workspace, the partition state in `workspace` is still in use then)."""
     import torch
     import torch.distributed as dist
     k = Kind(kind)
@@ -277,13 +332,50 @@ def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 
     allsamp = torch.cat([g[:s] for g, s in zip(gathered, sizes)], dim=0).contiguous()
     ops.local_sort(allsamp, k)
     samp_host = ops.to_host(allsamp)
-    picks = choose_splitters(samp_host, world)
-    if len(picks) != world - 1:  # no keys anywhere
+    halves = exchange is not None and overlap and 2 * world <= MAX_RANKS and hasattr(ops, "partition_exchange_part")
+    picks = choose_splitters(samp_host, 2 * world if halves else world)
+    if len(picks) != (2 * world if halves else world) - 1:  # no keys anywhere
         return ShardedResult(keys[:0], 0, [0] * world, [0] * world, np.zeros((0, kb), dtype=np.uint8))
-    splitters = np.ascontiguousarray(np.stack(picks))
+    fine = np.ascontiguousarray(np.stack(picks))
+    splitters = np.ascontiguousarray(fine[1::2]) if halves else fine  # the world - 1 range boundaries
     mark("splitters")
 
-    if exchange is not None:
+    if halves:
+        # 3''. count per SUB-range  4''. count matrix -> offsets of my keys in every sub-range
+        ws = ops.workspace_for(n_local, k, workspace)
+        counts = ops.partition_count(rows, k, fine, ws)
+        rws = [torch.zeros_like(counts) for _ in range(world)]
+        dist.all_gather(rws, counts, group=group)
+        cm2 = np.stack([ops.to_host(r) for r in rws])            # world x 2*world
+        cm = cm2[:, 0::2] + cm2[:, 1::2]                          # world x world, per destination rank
+        send_counts, recv_counts = exchange_plan(cm, rank)
+        n_out = sum(recv_counts)
+        mark("count")
+        if int(cm.sum(axis=0).max()) <= exchange.capacity:  # same decision on every rank
+            offs, first, second = halved_plan(cm2, rank)
+            offsets = torch.tensor(offs, dtype=torch.int64).to(rows.device)
+            owners = [j // 2 for j in range(2 * world)]
+            even = sum(1 << j for j in range(0, 2 * world, 2))
+            # 5''. first halves: K7 + barrier on this stream
+            ops.partition_exchange_part(rows, k, fine, ws, exchange, offsets, owners, even, False, 0)
+            mark("exchange")
+            # second halves on the side stream (after the first K7: they share its state in ws) ...
+            side = ops.side_stream()
+            ops.fork(side)
+            with ops.on(side):
+                ops.partition_exchange_part(rows, k, fine, ws, exchange, offsets, owners, even << 1, True, 1)
+            # ... while this stream sorts the first half, then the second once it is complete
+            n_a, n_b = first[rank], second[rank]
+            ws2 = ops.workspace_for(max(n_a, n_b), k, workspace2)
+            ops.local_sort(exchange.recv_rows[:n_a], k, ws2)
+            ops.join(side)
+            ops.local_sort(exchange.recv_rows[n_a:n_a + n_b], k, ws2)
+            mark("local_sort")
+            finish()
+            return ShardedResult(typed(exchange.recv_rows[:n_out]), n_out, send_counts, recv_counts, splitters)
+        # would overflow the receive buffers: the unfused path below, with the range splitters only
+
+    elif exchange is not None:
         # 3'. count  4'. count matrix -> where my keys start in every receive buffer
         ws = ops.workspace_for(n_local, k, workspace)
         counts = ops.partition_count(rows, k, splitters, ws)

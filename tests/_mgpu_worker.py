@@ -25,15 +25,15 @@ def main():
             a = rng.integers(0, 2**64, size=n, dtype=np.uint64)
             if case == "few_unique":
                 a = (a % 5) * 1000
-            for use_exchange in (True, False):
+            for use_exchange, overlap in ((True, False), (True, True), (False, False)):
                 keys = torch.from_numpy(a.copy()).to(dev)
-                res = mgpu.sort_sharded(keys, rs.Kind.U64, exchange=exchange if use_exchange else None)
+                res = mgpu.sort_sharded(keys, rs.Kind.U64, exchange=exchange if use_exchange else None, overlap=overlap)
                 mine = res.keys.cpu().numpy().copy()
                 gathered = [None] * world
                 dist.all_gather_object(gathered, (a, mine))
                 whole_in = np.concatenate([g[0] for g in gathered])
                 whole_out = np.concatenate([g[1] for g in gathered])
-                assert np.array_equal(whole_out, np.sort(whole_in)), (case, use_exchange)
+                assert np.array_equal(whole_out, np.sort(whole_in)), (case, use_exchange, overlap)
                 torch.cuda.synchronize()
                 dist.barrier()
         if rank == 0:

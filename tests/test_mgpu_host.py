@@ -78,6 +78,39 @@ class NumpyOps:
             recv[off: off + len(part)] = part
 
 
+    # overlapped exchange: one piece = the buckets of `bucket_mask`, bucket j into the
+    # receive buffer of rank owners[j]
+    def partition_exchange_part(self, rows, kind, splitters_host, workspace, exchange, offsets, owners, bucket_mask,
+                                again, channel):
+        a, dest = self._dest(rows, splitters_host)
+        world = dist.get_world_size()
+        mine = [[] for _ in range(world)]
+        for j, o in enumerate(owners):
+            if (bucket_mask >> j) & 1:
+                mine[o].append((int(offsets[j]), a[dest == j].copy()))
+        everyone = [None] * world
+        dist.all_gather_object(everyone, mine)
+        recv = exchange.recv_rows.numpy().reshape(-1).view(np.uint64)
+        me = dist.get_rank()
+        for sender in range(world):
+            for off, part in everyone[sender][me]:
+                assert off + len(part) <= exchange.capacity
+                recv[off: off + len(part)] = part
+
+    def side_stream(self):
+        return None
+
+    def fork(self, side):
+        pass
+
+    def join(self, side):
+        pass
+
+    def on(self, stream):
+        import contextlib
+        return contextlib.nullcontext()
+
+
 class FakeExchange:
     """Stands in for mgpu.PeerExchange: a local receive buffer of `capacity` keys."""
 
@@ -94,7 +127,7 @@ def _free_port():
     return port
 
 
-def _worker(rank, world, port, n_per_rank, mode, q, fused=False, capacity=0):
+def _worker(rank, world, port, n_per_rank, mode, q, fused=False, capacity=0, overlap=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -109,7 +142,7 @@ def _worker(rank, world, port, n_per_rank, mode, q, fused=False, capacity=0):
         keys = torch.from_numpy(a.copy())
         # int64 tensor holding u64 bit patterns < 2^63 (same order either way)
         exchange = FakeExchange(capacity) if fused else None
-        res = mgpu.sort_sharded(keys, Kind.U64, ops=NumpyOps(), samples_per_rank=512, exchange=exchange)
+        res = mgpu.sort_sharded(keys, Kind.U64, ops=NumpyOps(), samples_per_rank=512, exchange=exchange, overlap=overlap)
         if fused and capacity >= 2 * n_per_rank:  # the result must be a view of the receive buffer
             assert res.keys.data_ptr() == exchange.recv_rows.data_ptr()
         out = res.keys.numpy().copy()
@@ -118,16 +151,19 @@ def _worker(rank, world, port, n_per_rank, mode, q, fused=False, capacity=0):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mode,fused,capacity", [("uniform", False, 0), ("few_unique", False, 0), ("ragged", False, 0),
-                                                 ("uniform", True, 40_000), ("few_unique", True, 40_000),
-                                                 ("ragged", True, 40_000),
-                                                 ("uniform", True, 100)])  # too small: all ranks fall back together
-def test_sort_sharded_world2_gloo(mode, fused, capacity):
+@pytest.mark.parametrize("mode,fused,capacity,overlap", [
+    ("uniform", False, 0, False), ("few_unique", False, 0, False), ("ragged", False, 0, False),
+    ("uniform", True, 40_000, False), ("few_unique", True, 40_000, False), ("ragged", True, 40_000, False),
+    ("uniform", True, 100, False),  # too small: all ranks fall back together
+    # overlapped exchange: ranges cut in two, the halves sent as two pieces
+    ("uniform", True, 40_000, True), ("few_unique", True, 40_000, True), ("ragged", True, 40_000, True),
+    ("uniform", True, 100, True)])
+def test_sort_sharded_world2_gloo(mode, fused, capacity, overlap):
     world, n = 2, 20_000
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, n, mode, q, fused, capacity)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, mode, q, fused, capacity, overlap)) for r in range(world)]
     [p.start() for p in procs]
     got = {}
     for _ in range(world):
@@ -162,6 +198,10 @@ def test_sample_positions_and_splitters_are_deterministic():
     assert mgpu.send_offsets(cm, 0) == [0, 0, 0]
     assert mgpu.send_offsets(cm, 1) == [1, 2, 3]
     assert mgpu.send_offsets(cm, 2) == [5, 7, 9]
+    # halved ranges: 2 ranks x 4 sub-ranges; rank d's buffer = [sub-range 2d | sub-range 2d+1], each in sender order
+    cm2 = np.array([[1, 2, 3, 4], [5, 6, 7, 8]])
+    assert mgpu.halved_plan(cm2, 0) == ([0, 6, 0, 10], [6, 10], [8, 12])
+    assert mgpu.halved_plan(cm2, 1) == ([1, 8, 3, 14], [6, 10], [8, 12])
 
 
 def test_cuda_ops_refuse_to_run_without_a_gpu():

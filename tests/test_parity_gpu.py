@@ -413,8 +413,8 @@ def test_partition_by_splitters(kind, cuda):
     assert _ref.same_bits(d_in.cpu().numpy(), a)  # input untouched
 
 
-@pytest.mark.parametrize("kind", ["u32", "u64", "f64"])
-def test_partition_count_then_exchange_into_separate_buffers(kind, cuda):
+@pytest.mark.parametrize("kind,pieces", [("u32", 1), ("u64", 1), ("f64", 1), ("u64", 2), ("u32", 3)])
+def test_partition_count_then_exchange_into_separate_buffers(kind, pieces, cuda):
     """The fused multi-GPU form of K7 on one device: every destination has its own
     receive buffer ("peer" pointer) and this rank's keys start at a given offset in
     each, as if lower ranks had already claimed the space before it."""
@@ -449,9 +449,23 @@ def test_partition_count_then_exchange_into_separate_buffers(kind, cuda):
             .view(d_in.dtype) for r in range(nsplit + 1)]
     bases = (ctypes.c_void_p * (nsplit + 1))(*[b.data_ptr() for b in bufs])
     d_offs = torch.tensor(offs, dtype=torch.int64, device=cuda)
-    rc = L.b200sort_partition_exchange_device(d_in.data_ptr(), ws.data_ptr(), ws.numel(), n, int(k), spl.ctypes.data, nsplit,
-                                              bases, d_offs.data_ptr(), st)
-    assert rc == 0, L.b200sort_last_error()
+    if pieces == 1:
+        rc = L.b200sort_partition_exchange_device(d_in.data_ptr(), ws.data_ptr(), ws.numel(), n, int(k), spl.ctypes.data,
+                                                  nsplit, bases, d_offs.data_ptr(), st)
+        assert rc == 0, L.b200sort_last_error()
+    else:
+        # the overlapped exchange: the buckets go out in several launches over the same counts,
+        # each storing only the buckets of its mask (pieces == 3: one launch stores nothing new)
+        masks = {2: [0b0101, 0b1010], 3: [0b0001, 0b0110, 0b1000]}[pieces]
+        for i, m in enumerate(masks):
+            rc = L.b200sort_partition_exchange_part_device(d_in.data_ptr(), ws.data_ptr(), ws.numel(), n, int(k),
+                                                           spl.ctypes.data, nsplit, bases, d_offs.data_ptr(), m, int(i > 0), st)
+            assert rc == 0, L.b200sort_last_error()
+            if i == 0:  # the buckets of the later pieces are still untouched
+                torch.cuda.synchronize()
+                later = [r for r in range(nsplit + 1) if not (m >> r) & 1]
+                for r in later:
+                    assert bool((bufs[r].view(torch.uint8) == fill).all())
     torch.cuda.synchronize()
     pad = np.frombuffer(bytes([fill]) * a.itemsize, dtype=a.dtype)[0]
     for r in range(nsplit + 1):
