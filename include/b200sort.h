@@ -113,6 +113,17 @@ int b200sort_records_host(void *recs, size_t n, size_t rec_bytes, size_t key_off
  * (memset nodes not counted).  bench.py reports the delta as gpu_launches. */
 unsigned long long b200sort_launch_count(void);
 
+/* Test hooks for the K3 slow path.  A tile whose order check fails is re-ranked
+ * with ballots and rewritten; that has never been observed on B200, so tests
+ * force it: b200sort_debug_force_rerank(1) makes every tile of every later sort
+ * of this process take the slow path (0 restores).  b200sort_debug_reranked_tiles
+ * synchronises `stream` and returns in *out how many tiles of the LAST sort run
+ * on d_tmp (same n, kind; rec_bytes = 0 for key sorts, 8 / 16 for record sorts)
+ * took it. */
+void b200sort_debug_force_rerank(int on);
+int b200sort_debug_reranked_tiles(void *d_tmp, size_t tmp_bytes, size_t n, int kind, size_t rec_bytes, void *stream,
+                                  unsigned *out);
+
 /* Kernel-tuning override for sweeps: K3 variant index per element width.
  * key_bytes = 1, 2, 4, 8, 16 selects the key-only table of that width, 108 / 116
  * the tables of 8- / 16-byte records.  -1 restores the default.  Returns

@@ -208,6 +208,22 @@ def set_host_pipeline_min_bytes(nbytes: int) -> None:
     check(_ffi.lib().b200sort_set_host_pipeline_min_bytes(int(nbytes)))
 
 
+def debug_force_rerank(on: bool) -> None:
+    """Test hook: every K3 tile of every later sort takes the ballot re-rank slow path."""
+    _ffi.lib().b200sort_debug_force_rerank(1 if on else 0)
+
+
+def debug_reranked_tiles(workspace, n: int, kind, rec_bytes: int = 0) -> int:
+    """Tiles of the last sort run on `workspace` (a CUDA tensor) that took the slow path."""
+    import torch
+    out = ctypes.c_uint(0)
+    stream = torch.cuda.current_stream(workspace.device).cuda_stream
+    with torch.cuda.device(workspace.device):
+        check(_ffi.lib().b200sort_debug_reranked_tiles(workspace.data_ptr(), workspace.numel(), n, int(Kind(kind)), rec_bytes,
+                                                       ctypes.c_void_p(stream), ctypes.byref(out)))
+    return int(out.value)
+
+
 def num_variants(key_bytes_: int) -> int:
     return int(_ffi.lib().b200sort_num_variants(key_bytes_))
 

@@ -37,6 +37,8 @@ int cuda_fail(cudaError_t e, const char* what) {
                 std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")");
 }
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+std::atomic<int> g_force_rerank{0};
+bool force_rerank() { return g_force_rerank.load(std::memory_order_relaxed) != 0; }
 int variant_override(int family, int elem_bytes) {
     return g_variant[family][elem_bytes].load(std::memory_order_relaxed) - 1;
 }
@@ -538,6 +540,22 @@ int b200sort_partition_exchange_part_device(const void* d_in, void* d_tmp, size_
 }
 
 unsigned long long b200sort_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+void b200sort_debug_force_rerank(int on) { g_force_rerank.store(on ? 1 : 0, std::memory_order_relaxed); }
+
+int b200sort_debug_reranked_tiles(void* d_tmp, size_t tmp_bytes, size_t n, int kind, size_t rec_bytes, void* stream,
+                                  unsigned* out) {
+    if (!d_tmp || !out) return fail(B200SORT_ERR_INVALID_ARG, "null pointer");
+    *out = 0;
+    if (n == 0) return B200SORT_OK;
+    const size_t kb = b200sort_key_bytes(kind);
+    if (kb == 0) return fail(B200SORT_ERR_UNSUPPORTED_KIND, "unknown key kind " + std::to_string(kind));
+    SortCall c;
+    c.elems = d_tmp;  // not touched; only has to be non-null
+    c.ws = d_tmp; c.ws_bytes = tmp_bytes; c.n = n; c.st = static_cast<cudaStream_t>(stream);
+    c.phase = SortCall::PHASE_READ_STATS; c.out_stats = out;
+    return rec_bytes ? front_by_width<FAM_RECORDS>(rec_bytes, c) : front_by_width<FAM_KEYS>(kb, c);
+}
 
 int b200sort_set_variant(int key_bytes, int variant) {
     // key_bytes selects the key-only table of that width; 108 / 116 select the

@@ -110,6 +110,11 @@ int sort_front(const SortCall& c) {
     uint32_t* lookback = reinterpret_cast<uint32_t*>(ws + L.lb_off);
     uint32_t* stats = reinterpret_cast<uint32_t*>(ws + L.stats_off);
 
+    if (ph == SortCall::PHASE_READ_STATS) {
+        B200_CU(cudaStreamSynchronize(st));
+        B200_CU(cudaMemcpy(c.out_stats, stats, sizeof(unsigned), cudaMemcpyDeviceToHost));
+        return B200SORT_OK;
+    }
     PhaseTimer timer(c.out_ms != nullptr, st);
     timer.mark();
     if (do_zero) B200_CU(cudaMemsetAsync(ws + L.zero_off, 0, L.zero_bytes, st));
@@ -180,6 +185,7 @@ int sort_front(const SortCall& c) {
             a.lookback_half = (FAM == FAM_PARTITION) ? 0 : L.tiles_total * RADIX;
             a.ticket = tickets + (size_t)p * L.portions + q;
             a.stats = stats;
+            a.force_rerank = force_rerank() ? 1u : 0u;
             a.prm = prm;
             lb_cursor += a.num_tiles;
             B200_CU((launch_pass_idx<FAM, W>(variant, a, st)));

@@ -26,6 +26,7 @@ int fail(int code, const std::string& msg);
 int cuda_fail(cudaError_t e, const char* what);
 void count_launch();
 int variant_override(int family, int elem_bytes);  // -1 = library default
+bool force_rerank();                               // test hook (b200sort_debug_force_rerank)
 
 #define B200_CU(call)                                               \
     do {                                                            \
@@ -212,7 +213,10 @@ struct SortCall {
     //   PHASE_COUNT_BEGIN / _PART / _END: PHASE_COUNT in pieces -- zero the state, histogram
     //                 elements [part_off, part_off + part_n) (any number of times), then scan + plan;
     //                 lets the host path count chunks while later chunks are still being copied in
-    enum { PHASE_ALL = 0, PHASE_COUNT = 1, PHASE_SCATTER = 2, PHASE_COUNT_BEGIN = 3, PHASE_COUNT_PART = 4, PHASE_COUNT_END = 5 };
+    //   PHASE_READ_STATS: no kernel; synchronises and copies the workspace's counter of re-ranked tiles to *out_stats
+    enum { PHASE_ALL = 0, PHASE_COUNT = 1, PHASE_SCATTER = 2, PHASE_COUNT_BEGIN = 3, PHASE_COUNT_PART = 4, PHASE_COUNT_END = 5,
+           PHASE_READ_STATS = 6 };
+    unsigned* out_stats = nullptr;
     int phase = PHASE_ALL;
     size_t part_off = 0, part_n = 0;
     unsigned bucket_mask = 0xFFFFFFFFu;              // PHASE_SCATTER: buckets this launch stores (bit r = bucket r)

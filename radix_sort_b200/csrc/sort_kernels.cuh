@@ -268,6 +268,7 @@ struct PassArgs {
     size_t lookback_half;                // words between the halves; 0 = one half only (single-pass partition)
     uint32_t* ticket;                    // tile-id dispenser, zeroed
     uint32_t* stats;                     // [0] tiles that took the re-rank fallback
+    uint32_t force_rerank;               // test hook: every tile takes the re-rank fallback (b200sort_debug_force_rerank)
     typename Tr::Params prm;
 };
 
@@ -282,7 +283,10 @@ struct PassSmem {
     static constexpr size_t GPTR_BYTES = (size_t)RADIX * sizeof(unsigned long long);
     static constexpr size_t EXCL_BYTES = (size_t)RADIX * sizeof(uint32_t);
     static constexpr size_t CNT_BYTES = (size_t)RADIX * sizeof(uint32_t);
-    static constexpr size_t AUX_BYTES = HIST_BYTES + GPTR_BYTES + EXCL_BYTES + CNT_BYTES + 64 + 16;
+    // records: one word {digit:16, source slot:16} per tile slot, the stability check of the write-out
+    static constexpr size_t ENT_BYTES = Tr::NEEDS_STABLE ? (size_t)TILE * sizeof(uint32_t) : 0;
+    static_assert(!Tr::NEEDS_STABLE || TILE <= 65536, "source slots are kept in 16 bits");
+    static constexpr size_t AUX_BYTES = HIST_BYTES + GPTR_BYTES + EXCL_BYTES + CNT_BYTES + 64 + 16 + ENT_BYTES;
     static constexpr size_t TOTAL = TILE_BYTES + AUX_BYTES;
 };
 
@@ -296,6 +300,7 @@ struct PassShared {
     uint32_t* excl;                 // [256] keys of the tile with a smaller digit
     uint32_t* cnt;                  // [256] keys of the tile with this digit
     uint32_t* misc;                 // [0..1] tickets, [2..9] warp totals of the digit scan
+    uint32_t* ent;                  // [TILE] records only: (digit << 16) | source slot of the record in this tile slot
     __device__ __forceinline__ PassShared() {}
     __device__ __forceinline__ PassShared(unsigned char* raw, size_t tile_bytes_total) {
         tile = reinterpret_cast<typename Tr::elem_t*>(raw);
@@ -305,6 +310,7 @@ struct PassShared {
         excl = reinterpret_cast<uint32_t*>(aux + SM::HIST_BYTES + SM::GPTR_BYTES);
         cnt = excl + RADIX;
         misc = cnt + RADIX;
+        ent = misc + 20;  // misc holds 64 + 16 bytes
     }
 };
 
@@ -457,11 +463,14 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
             E below{};  // the key one row down; past the last row: the next warp's first key (lane 0 only)
             if (j + 1 < ITEMS) {
                 if (FULL || idx + 32 < n_valid) below = sh.tile[idx + 32];
-            } else if (VERIFY) {
+            } else if (VERIFY && !Tr::NEEDS_STABLE) {
                 if (lane == 0 && idx + 32 < n_valid) below = sh.tile[idx + 32];
             }
             E key = cur;
-            if constexpr (VERIFY) {
+            if constexpr (VERIFY && Tr::NEEDS_STABLE) {
+                // records: {digit, source slot} must rise strictly along the tile (stable by digit)
+                if (idx + 1 < n_valid) bad |= sh.ent[idx] >= sh.ent[idx + 1];
+            } else if constexpr (VERIFY) {
                 const E nxt = shfl_elem(lane == 0 ? below : key, (lane + 1) & 31);
                 if (idx + 1 < n_valid) bad |= Tr::prefix_less(nxt, key, a.pass, a.prm);
             }
@@ -478,7 +487,11 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
             const uint32_t idx = (uint32_t)j * THREADS + tid;
             if (FULL || idx < n_valid) {
                 E key = sh.tile[idx];
-                if (VERIFY && idx + 1 < n_valid) bad |= Tr::prefix_less(sh.tile[idx + 1], key, a.pass, a.prm);
+                if constexpr (VERIFY && Tr::NEEDS_STABLE) {
+                    if (idx + 1 < n_valid) bad |= sh.ent[idx] >= sh.ent[idx + 1];
+                } else if constexpr (VERIFY) {
+                    if (idx + 1 < n_valid) bad |= Tr::prefix_less(sh.tile[idx + 1], key, a.pass, a.prm);
+                }
                 const unsigned d = Tr::digit(key, a.pass, a.prm);
                 if (xf_out) key = Tr::xform_out(key, a.prm);
                 *reinterpret_cast<E*>(sh.gptr[d] + (unsigned long long)idx * sizeof(E)) = key;
@@ -556,15 +569,8 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
 
     // ---- 1. count: the warp's counters become its digit histogram
     uint32_t* my_hist = sh.warp_hist + warp * RADIX;
-    uint32_t rank[Tr::NEEDS_STABLE ? ITEMS : 1];
     unsigned code[Tr::FEW_BUCKETS ? (ITEMS + 7) / 8 : 1] = {};  // FEW_BUCKETS: 4-bit digit of every key
-    if (Tr::NEEDS_STABLE) {
-        const unsigned lane_lt = (1u << lane) - 1u;
-#pragma unroll
-        for (int i = 0; i < ITEMS; ++i)
-            rank[Tr::NEEDS_STABLE ? i : 0] =
-                ballot_rank<FULL>(Tr::digit(e[i], pass, a.prm), FULL || wbase + i * 32 < tile_n, my_hist, lane, lane_lt);
-    } else if constexpr (Tr::FEW_BUCKETS) {
+    if constexpr (Tr::FEW_BUCKETS) {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
             if (FULL || wbase + i * 32 < tile_n) {
@@ -578,7 +584,7 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
             if (FULL || wbase + i * 32 < tile_n) atomicAdd(&my_hist[hidx(Tr::digit(e[i], pass, a.prm))], 1u);
     }
     __syncthreads();
-    if constexpr (!Tr::NEEDS_STABLE && !Tr::FEW_BUCKETS) {
+    if constexpr (!Tr::FEW_BUCKETS) {
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) launder(e[i]);
     }
@@ -683,14 +689,10 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
                     sh.tile[atomicAdd(&my_hist[hidx(d)], 1u)] = e[i];
                 }
         }
-    } else if constexpr (Tr::NEEDS_STABLE || (ABL & 8) != 0) {
+    } else if constexpr ((ABL & 8) != 0) {  // timing ablation: identity slots
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
-            if (FULL || wbase + i * 32 < tile_n) {
-                const unsigned d = Tr::digit(e[i], pass, a.prm);
-                const uint32_t slot = (ABL & 8) ? wbase + i * 32 + (d & 0u) : rank[Tr::NEEDS_STABLE ? i : 0] + my_hist[hidx(d)];
-                sh.tile[slot] = e[i];
-            }
+            if (FULL || wbase + i * 32 < tile_n) sh.tile[wbase + i * 32] = e[i];
     } else {
         const uint32_t domw = sh.misc[10];
         // no digit above half of the tile: the digit of the warp's first key stands in
@@ -709,7 +711,10 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
             uint32_t slot = dom_slot + (uint32_t)__popc(m & lane_lt);
             dom_slot += (uint32_t)__popc(m);
             if (valid && !is_dom) slot = atomicAdd(&my_hist[hidx(d)], 1u);
-            if (valid) sh.tile[slot] = e[i];
+            if (valid) {
+                sh.tile[slot] = e[i];
+                if constexpr (Tr::NEEDS_STABLE) sh.ent[slot] = (d << 16) | (wbase + (uint32_t)i * 32u);
+            }
         }
     }
     after_scatter();  // e[] is dead from here on: the streaming kernel re-fills it with the next tile
@@ -719,7 +724,7 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
 
     // ---- coalesced run write-out; key-only passes check the order of the tile
     if (ABL & 4) return false;
-    if (Tr::NEEDS_STABLE || pass == 0 || (ABL & 2)) {
+    if ((!Tr::NEEDS_STABLE && pass == 0) || (ABL & 2)) {
         write_out<Tr, WORKERS, ITEMS, FULL, false>(sh, a, pp.xf_out, tile_n, tid);
         return false;
     }
@@ -773,8 +778,9 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
             if (wbase + i * 32 < tile_n) e[i] = ld_elem(src_tile + wbase + i * 32);
         bad = rank_and_scatter<Tr, THREADS, ITEMS, false, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, NoHook{});
     }
-    if (Tr::NEEDS_STABLE || a.pass == 0 || (ABL & 31) != 0) return;  // (bits 0..4 are timing ablations: results wrong on purpose)
-    if (!__syncthreads_or(bad)) return;
+    if ((ABL & 31) != 0) return;  // (bits 0..4 are timing ablations: results wrong on purpose)
+    if (!Tr::NEEDS_STABLE && a.pass == 0 && !a.force_rerank) return;  // no order to check, and bad == false
+    if (!__syncthreads_or(bad || a.force_rerank)) return;
     if (tid == 0) atomicAdd(a.stats, 1u);
     rerank_tile<Tr, THREADS, ITEMS>(sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
 }

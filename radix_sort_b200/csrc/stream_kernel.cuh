@@ -93,9 +93,9 @@ onesweep_stream_kernel(const __grid_constant__ PassArgs<Tr> a) {
             bad = rank_and_scatter<Tr, THREADS, ITEMS, false, LBB, ABL>(sh, a, pp, e, dst, tile, tile_n, park_ticket, prefetch);
         // end-of-tile barrier: the write-out has read sh.tile / sh.gptr before the
         // next tile's phases overwrite them
-        if (Tr::NEEDS_STABLE || a.pass == 0) {
+        if (!Tr::NEEDS_STABLE && a.pass == 0 && !a.force_rerank) {
             __syncthreads();
-        } else if (__syncthreads_or(bad)) {
+        } else if (__syncthreads_or(bad || a.force_rerank)) {
             if (tid == 0) atomicAdd(a.stats, 1u);
             rerank_tile<Tr, THREADS, ITEMS>(sh, &a, src_tile, tile_n, pp.xf_in, pp.xf_out);
 #pragma unroll

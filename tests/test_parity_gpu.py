@@ -269,6 +269,63 @@ def test_records_stable_host_and_device(key_kind, dt, key_col, cuda):
     assert _ref.same_bits(t.cpu().numpy(), want)
 
 
+# ---- the K3 slow path (ballot re-rank of a tile whose order check failed) ---------------
+# It has never fired on B200 (the fast ranker's lane-order assumption holds), so tests force it.
+
+@pytest.mark.parametrize("kind", ["u8", "u16", "u32", "i64", "f64", "u128"])
+def test_forced_rerank_keys(kind, cuda):
+    import torch
+    k = _kind(kind)
+    n = 300_007
+    a = _ref.random_keys(kind, n, seed=5)
+    want = _ref.expected_sorted(a, kind)
+    rs.debug_force_rerank(True)
+    try:
+        for variant in range(rs.num_variants(rs.key_bytes(k))):
+            rs.set_variant(rs.key_bytes(k), variant)
+            t = _to_device(a, cuda)
+            ws = torch.empty(rs.temp_bytes(n, k), dtype=torch.uint8, device=cuda)
+            rs.radix_sort(t, k, workspace=ws)
+            torch.cuda.synchronize()
+            assert _ref.same_bits(t.cpu().numpy(), want), f"variant {variant}"
+            assert rs.debug_reranked_tiles(ws, n, k) > 0, "the slow path did not run"
+    finally:
+        rs.set_variant(rs.key_bytes(k), -1)
+        rs.debug_force_rerank(False)
+    t = _to_device(a, cuda)
+    ws = torch.empty(rs.temp_bytes(n, k), dtype=torch.uint8, device=cuda)
+    rs.radix_sort(t, k, workspace=ws)
+    torch.cuda.synchronize()
+    assert rs.debug_reranked_tiles(ws, n, k) == 0, "a tile failed its order check on the fast path"
+
+
+@pytest.mark.parametrize("key_kind,dt", [("u32", np.uint32), ("f64", np.float64)])
+def test_forced_rerank_records_stay_stable(key_kind, dt, cuda):
+    import torch
+    rng = np.random.default_rng(123)
+    n = 200_003
+    kb = np.dtype(dt).itemsize
+    udt = np.uint32 if kb == 4 else np.uint64
+    recs = np.empty((n, 2), dtype=udt)
+    recs[:, 0] = rng.integers(0, 2**(8 * kb), size=n, dtype=np.uint64).astype(udt) & udt(0xFF0000FF if kb == 4 else 0xFF000000000000FF)
+    recs[:, 1] = np.arange(n, dtype=udt)
+    want = _ref.expected_sorted_records(recs.view(dt), key_kind, 0)
+    k = _kind(key_kind)
+    L = _ffi.lib()
+    for force in (True, False):
+        rs.debug_force_rerank(force)
+        try:
+            t = torch.from_numpy(recs.view(np.int32 if kb == 4 else np.int64)).to(cuda)
+            ws = torch.empty(int(L.b200sort_records_temp_bytes(n, 2 * kb, int(k))), dtype=torch.uint8, device=cuda)
+            rs.radix_sort_records(t, k, key_off=0, workspace=ws)
+            torch.cuda.synchronize()
+            assert _ref.same_bits(t.cpu().numpy(), want), f"forced={force}"
+            took = rs.debug_reranked_tiles(ws, n, k, rec_bytes=2 * kb)
+            assert (took > 0) == force, f"forced={force}: {took} tiles took the slow path"
+        finally:
+            rs.debug_force_rerank(False)
+
+
 def test_demo_shapes_pairs_payload_zero(cuda):
     # main.rs:101-126 + distr.rs:42-52: KeyUniform pairs (random key, payload 0)
     for udt, kind, oracle_kind in ((np.uint32, rs.Kind.U32, "pair_u32"), (np.uint64, rs.Kind.U64, "pair_u64")):
