@@ -229,9 +229,16 @@ scan_plan_kernel(const unsigned long long* __restrict__ hist, unsigned long long
 //     0..pass.  The write-out loop checks exactly that (one neighbour read per
 //     key); a tile that fails is re-ranked by rerank_tile() and rewritten, and
 //     counted in stats[0].
-//   * records (NEEDS_STABLE) always rank with ballots: 8 ballots give the lanes
-//     holding the same digit, rank = leader's counter + lower lanes of the group,
-//     lane-ordered by construction.
+//   * records (NEEDS_STABLE) need stability proper, and equal keys with different
+//     payloads cannot be told apart by comparing keys.  So the scatter also drops one
+//     word per tile slot, (digit << 16) | source slot of the record, into sh.ent; the
+//     tile is stably sorted by digit iff those words rise strictly along it, which the
+//     write-out checks (two 1-wavefront loads per warp instruction).  A failing tile
+//     takes the same slow path.  (Ranking every record tile with ballots -- 8 ballots
+//     give the lanes holding the same digit, lane-ordered by construction -- was the
+//     first version: (u32,u32) 39.7 -> 46.9 Grecords/s without it.)
+//   * rerank_tile(), the slow path, ranks with those ballots.  Tests force it
+//     (b200sort_debug_force_rerank) and read the counter (b200sort_debug_reranked_tiles).
 //
 // Look-back.  With C tiles in flight and a tile started every g = T_tile / C, a
 // walk that pays one L2 round trip l per predecessor settles at a depth of about
