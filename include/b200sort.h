@@ -121,6 +121,10 @@ unsigned long long b200sort_launch_count(void);
  * on d_tmp (same n, kind; rec_bytes = 0 for key sorts, 8 / 16 for record sorts)
  * took it. */
 void b200sort_debug_force_rerank(int on);
+/* Slices of at most 4096 elements are sorted by one launch of one CTA (all digit
+ * passes in shared memory) instead of the K1-K2-K3 sequence; 0 turns that off so
+ * that tests can drive the big path at small sizes too (1 restores). */
+void b200sort_debug_small_sort(int on);
 int b200sort_debug_reranked_tiles(void *d_tmp, size_t tmp_bytes, size_t n, int kind, size_t rec_bytes, void *stream,
                                   unsigned *out);
 

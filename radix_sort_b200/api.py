@@ -213,6 +213,11 @@ def debug_force_rerank(on: bool) -> None:
     _ffi.lib().b200sort_debug_force_rerank(1 if on else 0)
 
 
+def debug_small_sort(on: bool) -> None:
+    """Test hook: False sends slices of <= 4096 elements through the big K1-K2-K3 path too."""
+    _ffi.lib().b200sort_debug_small_sort(1 if on else 0)
+
+
 def debug_reranked_tiles(workspace, n: int, kind, rec_bytes: int = 0) -> int:
     """Tiles of the last sort run on `workspace` (a CUDA tensor) that took the slow path."""
     import torch

@@ -91,6 +91,25 @@ int sort_front(const SortCall& c) {
         return fail(B200SORT_ERR_INVALID_ARG, "keys not aligned to the element size");
     if (((uintptr_t)c.ws % 256) != 0) return fail(B200SORT_ERR_INVALID_ARG, "workspace not 256-byte aligned");
 
+    // small slices: the whole sort in one launch of one CTA (sort_kernels.cuh, small_sort_kernel)
+    if constexpr (FAM != FAM_PARTITION) {
+        if (ph == SortCall::PHASE_ALL && n <= (size_t)SmallSmem<Tr>::TILE && !c.out_ms && small_sort_enabled()) {
+            auto k = small_sort_kernel<Tr>;
+            constexpr size_t SS = SmallSmem<Tr>::TOTAL;
+            static std::atomic<unsigned> small_configured{0};  // bit per device
+            int dev = 0;
+            cudaGetDevice(&dev);
+            if (SS > 48 * 1024 && !(small_configured.load(std::memory_order_acquire) & (1u << (dev & 31)))) {
+                B200_CU(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS));
+                small_configured.fetch_or(1u << (dev & 31), std::memory_order_release);
+            }
+            k<<<1, SMALL_THREADS, SS, st>>>(d_elems, (uint32_t)n, prm, (c.flags & B200SORT_FLAG_NO_SKIP) ? 1 : 0);
+            count_launch();
+            B200_CU(cudaGetLastError());
+            return B200SORT_OK;
+        }
+    }
+
     int variant = variant_override(FAM, W);
     if (variant < 0 || variant >= num_variants<FAM, W>()) variant = 0;
     const VariantDesc vd = Variants<FAM, W>::v[variant];

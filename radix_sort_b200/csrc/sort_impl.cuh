@@ -27,6 +27,7 @@ int cuda_fail(cudaError_t e, const char* what);
 void count_launch();
 int variant_override(int family, int elem_bytes);  // -1 = library default
 bool force_rerank();                               // test hook (b200sort_debug_force_rerank)
+bool small_sort_enabled();                         // test hook (b200sort_debug_small_sort)
 
 #define B200_CU(call)                                               \
     do {                                                            \

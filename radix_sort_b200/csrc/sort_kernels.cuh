@@ -793,6 +793,88 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
 }
 
 // ---------------------------------------------------------------------------
+// Small sorts: n <= SMALL_THREADS * SMALL_ITEMS elements in ONE launch of one CTA.
+// The multi-kernel sequence (memset, K1, K2, D x K3, copy-back) is launch-bound
+// below ~1e5 keys (75 us for 1000 u32 keys, 125 us for u64: r01 small-n sweep); a
+// drop-in for slice.radix_sort() is called on small slices too.  The keys stay in
+// registers across the passes; every pass ranks them with the ballot ranker (stable
+// by construction, so the same code serves records), scatters them into shared
+// memory and reads them back in slot order.  A digit on which all keys agree is
+// skipped, as K2 does for the big path.
+// ---------------------------------------------------------------------------
+constexpr int SMALL_THREADS = 512;
+constexpr int SMALL_ITEMS = 8;
+
+template <typename Tr>
+struct SmallSmem {
+    static constexpr int TILE = SMALL_THREADS * SMALL_ITEMS;
+    static constexpr size_t TILE_BYTES = (size_t)TILE * sizeof(typename Tr::elem_t);
+    static constexpr size_t TOTAL = TILE_BYTES + (size_t)(SMALL_THREADS / 32) * RADIX * sizeof(uint32_t) + 64;
+};
+
+template <typename Tr>
+__global__ void __launch_bounds__(SMALL_THREADS, 1)
+small_sort_kernel(typename Tr::elem_t* __restrict__ keys, uint32_t n, typename Tr::Params prm, int no_skip) {
+    using E = typename Tr::elem_t;
+    constexpr int ITEMS = SMALL_ITEMS;
+    constexpr int WARPS = SMALL_THREADS / 32;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    E* tile = reinterpret_cast<E*>(smem_raw);
+    uint32_t* warp_hist = reinterpret_cast<uint32_t*>(smem_raw + SmallSmem<Tr>::TILE_BYTES);
+    uint32_t* misc = warp_hist + WARPS * RADIX;  // [0..7] warp totals of the digit scan
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lane_lt = (1u << lane) - 1u;
+    const uint32_t wbase = (uint32_t)warp * 32u * ITEMS + (uint32_t)lane;  // warp-striped: slot order == memory order
+    uint32_t* my_hist = warp_hist + warp * RADIX;
+
+    E e[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i)
+        if (wbase + i * 32 < n) e[i] = Tr::xform_in(ld_elem(keys + wbase + i * 32), prm);
+
+    for (int pass = 0; pass < Tr::DIGITS; ++pass) {
+#pragma unroll
+        for (int i = lane; i < RADIX; i += 32) my_hist[i] = 0;
+        __syncwarp();
+        uint32_t rank[ITEMS];
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+            rank[i] = ballot_rank<false>(Tr::digit(e[i], pass, prm), wbase + i * 32 < n, my_hist, lane, lane_lt);
+        __syncthreads();
+        // thread d owns digit d: count over the warps, exclusive scan over the digits
+        uint32_t count = 0, incl = 0;
+        if (tid < RADIX) count = column_total<WARPS>(warp_hist, tid);
+        incl = count;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL_MASK, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31 && warp < RADIX / 32) misc[warp] = incl;
+        const bool constant = __syncthreads_or(tid < RADIX && count == n) != 0;  // one digit holds every key
+        if (tid < RADIX) {
+            uint32_t base = 0;
+#pragma unroll
+            for (int w = 0; w < RADIX / 32; ++w) base += (w < warp) ? misc[w] : 0u;
+            column_bases<WARPS>(warp_hist, tid, base + incl - count);
+        }
+        __syncthreads();
+        if (constant && !no_skip) continue;  // the pass is the identity (CTA-uniform)
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+            if (wbase + i * 32 < n) tile[rank[i] + my_hist[hidx(Tr::digit(e[i], pass, prm))]] = e[i];
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+            if (wbase + i * 32 < n) e[i] = tile[wbase + i * 32];
+        // (the next scatter into `tile` is two barriers away)
+    }
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i)
+        if (wbase + i * 32 < n) keys[wbase + i * 32] = Tr::xform_out(e[i], prm);
+}
+
+// ---------------------------------------------------------------------------
 // Odd number of executed passes: the result sits in tmp (mod.rs:170-174).
 // Exits at once when the plan says the result is already in the caller's buffer.
 // ---------------------------------------------------------------------------

@@ -96,8 +96,42 @@ EDGE_SIZES = [1, 2, 31, 32, 33, 95, 96, 97, 255, 256, 257, 3071, 3072, 3073, 614
 
 @pytest.mark.parametrize("kind", _ref.KINDS)
 def test_device_path_edge_sizes(kind, cuda):
-    for n in EDGE_SIZES:
+    for n in EDGE_SIZES + [4095, 4096, 4097]:  # 4096: the largest slice the one-CTA small sort takes
         _check_device(_ref.random_keys(kind, n, seed=n), kind, cuda)
+
+
+@pytest.mark.parametrize("kind", _ref.KINDS)
+def test_small_sizes_through_the_big_path(kind, cuda):
+    # slices of <= 4096 elements normally take the one-CTA small sort: switch it off so that
+    # the K1-K2-K3 sequence keeps its coverage of ragged single tiles
+    rs.debug_small_sort(False)
+    try:
+        for n in [s for s in EDGE_SIZES if s <= 4096] + [4095, 4096]:
+            _check_device(_ref.random_keys(kind, n, seed=n), kind, cuda)
+    finally:
+        rs.debug_small_sort(True)
+
+
+@pytest.mark.parametrize("small", [True, False])
+@pytest.mark.parametrize("key_kind,dt", [("u32", np.uint32), ("i64", np.int64), ("f32", np.float32)])
+def test_small_record_slices_stay_stable(key_kind, dt, small, cuda):
+    import torch
+    kb = np.dtype(dt).itemsize
+    udt = np.uint32 if kb == 4 else np.uint64
+    rs.debug_small_sort(small)
+    try:
+        for n in (1, 2, 33, 257, 1000, 4095, 4096, 4097):
+            rng = np.random.default_rng(n)
+            recs = np.empty((n, 2), dtype=udt)
+            recs[:, 0] = rng.integers(0, 2**(8 * kb), size=n, dtype=np.uint64).astype(udt) & udt(0x80000003 if kb == 4 else 0x8000000000000003)
+            recs[:, 1] = np.arange(n, dtype=udt)
+            want = _ref.expected_sorted_records(recs.view(dt), key_kind, 0)
+            t = torch.from_numpy(recs.view(np.int32 if kb == 4 else np.int64)).to(cuda)
+            rs.radix_sort_records(t, _kind(key_kind), key_off=0)
+            torch.cuda.synchronize()
+            assert _ref.same_bits(t.cpu().numpy(), want), f"n={n}"
+    finally:
+        rs.debug_small_sort(True)
 
 
 @pytest.mark.parametrize("kind", _ref.KINDS)
@@ -185,6 +219,17 @@ def test_degenerate_inputs_skip_and_no_skip(kind, cuda):
         a = np.ascontiguousarray(a)
         _check_device(a, kind, cuda)
         _check_device(a, kind, cuda, flags=rs.FLAG_NO_SKIP)
+
+
+@pytest.mark.parametrize("kind", ["u8", "u32", "i64", "f32", "u128"])
+def test_degenerate_small_slices(kind, cuda):
+    # the one-CTA small sort skips a digit on which all keys agree: with and without the skip
+    for n in (1, 37, 3000, 4096):
+        base = _ref.random_keys(kind, n, seed=n + 3)
+        for a in (np.repeat(base[:1], n, axis=0), base[np.arange(n) % 2]):
+            a = np.ascontiguousarray(a)
+            _check_device(a, kind, cuda)
+            _check_device(a, kind, cuda, flags=rs.FLAG_NO_SKIP)
 
 
 def test_known_answer_float_order(cuda):
