@@ -92,16 +92,16 @@ struct VariantEntry {
     static cudaError_t launch(const PassArgs<typename FamilyTraits<FAM, W>::type>& a, cudaStream_t st);
 };
 
-template <typename Tr, int KERNEL, int THREADS, int ITEMS, int MINB, int LBT>
+template <typename Tr, int KERNEL, int THREADS, int ITEMS, int MINB, int LBB_ABL>
 struct PassLauncher {
     using SM = PassSmem<Tr, THREADS, ITEMS>;
     static_assert(KERNEL == 0 || KERNEL == 3, "kernel ids: 0 one tile per CTA, 3 streaming");
     static constexpr int BLOCK = THREADS;
-    static constexpr int LBB = (LBT & 255) > 0 ? (LBT & 255) : LB_BATCH;
+    static constexpr int LBB = (LBB_ABL & 255) > 0 ? (LBB_ABL & 255) : LB_BATCH;  // bits 8+: timing-ablation mask
     static constexpr size_t SMEM = SM::TOTAL;
     static auto kernel() {
-        if constexpr (KERNEL == 3) return onesweep_stream_kernel<Tr, THREADS, ITEMS, MINB, LBB, (LBT >> 8)>;
-        else return onesweep_pass_kernel<Tr, THREADS, ITEMS, MINB, LBB, (LBT >> 8)>;
+        if constexpr (KERNEL == 3) return onesweep_stream_kernel<Tr, THREADS, ITEMS, MINB, LBB, (LBB_ABL >> 8)>;
+        else return onesweep_pass_kernel<Tr, THREADS, ITEMS, MINB, LBB, (LBB_ABL >> 8)>;
     }
     // per-device one-time setup: opt in to the dynamic shared memory, read the occupancy
     static cudaError_t prepare(int* resident) {

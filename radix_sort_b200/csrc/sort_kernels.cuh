@@ -254,7 +254,7 @@ scan_plan_kernel(const unsigned long long* __restrict__ hist, unsigned long long
 //                           keep the next tile's loads in flight.
 // Two TMA-ring kernels (cp.async.bulk + mbarrier, look-back in dedicated warps,
 // deferred write-out) were built and measured 10-40 % slower on every width
-// (profiles/r01_sweep_v5*, v13*, v16*); they were removed after commit 1a4e2dd --
+// (profiles/r01_sweep_v5*, v13*, v16*); they were removed after commit 823d302 --
 // the polling warps and the second tile buffer cost more than the overlap gained.
 // ---------------------------------------------------------------------------
 template <typename Tr>
