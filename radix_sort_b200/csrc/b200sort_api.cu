@@ -170,6 +170,24 @@ struct StreamGuard {
     ~StreamGuard() { if (st) cudaStreamDestroy(st); }
 };
 
+// The plain round trip runs on one non-blocking stream per (host thread, device), created
+// on first use and kept: cudaStreamCreate + cudaStreamDestroy per call was a third of the
+// 143 us a 1000-key host slice took.  A thread runs one host sort at a time, so the stream
+// is never shared; it is deliberately not destroyed at thread exit (the driver may be gone).
+cudaError_t thread_stream(cudaStream_t* out) {
+    thread_local cudaStream_t streams[32] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    cudaStream_t& s = streams[dev & 31];
+    if (!s) {
+        e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
+        if (e != cudaSuccess) { s = nullptr; return e; }
+    }
+    *out = s;
+    return cudaSuccess;
+}
+
 // copy in, sort, copy out; `sort` is called with (device elems, workspace, workspace bytes, stream)
 template <typename SortFn>
 int host_roundtrip(void* host, size_t bytes, size_t ws_bytes, SortFn sort) {
@@ -177,8 +195,8 @@ int host_roundtrip(void* host, size_t bytes, size_t ws_bytes, SortFn sort) {
     void* block = nullptr;
     int rc = pool_acquire(data_bytes + ws_bytes, &block);
     if (rc) return rc;
-    StreamGuard sg;
-    cudaError_t e = cudaStreamCreateWithFlags(&sg.st, cudaStreamNonBlocking);
+    struct { cudaStream_t st = nullptr; } sg;
+    cudaError_t e = thread_stream(&sg.st);
     if (e != cudaSuccess) { pool_release(block); return cuda_fail(e, "cudaStreamCreate"); }
     unsigned char* d = static_cast<unsigned char*>(block);
     // large pageable slices (a plain Vec<T>) go through the library's pinned bounce
