@@ -237,11 +237,15 @@ int host_roundtrip(void* host, size_t bytes, size_t ws_bytes, SortFn sort) {
 // The plain round trip serialises copy-in, sort and copy-out: 8 GB + 8 GB over
 // PCIe around a 39 ms sort.  The copy-in cannot overlap the sort (every pass
 // needs all keys), but the copy-out can: split the keys into 16 key ranges
-// first (one K7 pass with splitters sampled from the host buffer), sort the
-// ranges one after the other, and start the device->host copy of a range as
-// soon as it is sorted, on a second stream.  The ranges are contiguous and in
-// order in the partition output, so the host buffer ends up exactly as the plain
-// path leaves it.
+// (splitters sampled from the host buffer), sort the ranges one after the other,
+// and start the device->host copy of a range as soon as it is sorted, on a second
+// stream.  The split itself hides under the copy-in: the keys arrive in 16 chunks
+// and each chunk is split by one K7 run as it lands, into its own slice of a
+// second buffer.  After the last byte only that chunk's split (0.6 ms at 1 B u64)
+// is left; a range is then 16 pieces, gathered into the freed input buffer by
+// device copies right before its sort (0.3 ms per range, behind the copy-out of
+// the range before it).  The gathered ranges are contiguous and in order, so the
+// host buffer ends up exactly as the plain path leaves it.
 std::atomic<size_t> g_pipeline_min_bytes{(size_t)64 << 20};
 constexpr int PIPE_GROUPS = MAX_SPLITTERS + 1;
 
@@ -275,10 +279,15 @@ int keys_host_pipelined(void* host, size_t n, int kind) {
     const size_t kb = b200sort_key_bytes(kind);
     const size_t bytes = n * kb;
     const size_t data = align_up(bytes, 256);
-    const size_t ws_part = align_up(temp_by_width<FAM_PARTITION>(kb, n), 256);
-    const size_t counts_bytes = 256;
+    constexpr int CHUNKS = 16;
+    const size_t per_chunk = ((n + CHUNKS - 1) / CHUNKS + 4095) / 4096 * 4096;  // whole 16-byte vectors for K1
+    const size_t ws_part = align_up(temp_by_width<FAM_PARTITION>(kb, per_chunk), 256);
+    const size_t counts_bytes = align_up((size_t)CHUNKS * PIPE_GROUPS * 8, 256);
+    // workspace of the range sorts, sized for ranges up to 1.25x the even share; a more
+    // skewed split takes a second block once the counts are known
+    const size_t ws_sort_cap = align_up(b200sort_temp_bytes(n / PIPE_GROUPS + n / (4 * PIPE_GROUPS) + 4096, kind), 256);
     void* block = nullptr;
-    int rc = pool_acquire(2 * data + ws_part + counts_bytes, &block);
+    int rc = pool_acquire(2 * data + ws_part + counts_bytes + ws_sort_cap, &block);
     if (rc) return rc;
     struct Cleanup {
         void* block; void* extra = nullptr; cudaStream_t s = nullptr, c = nullptr; cudaEvent_t ev[PIPE_GROUPS] = {};
@@ -307,14 +316,14 @@ int keys_host_pipelined(void* host, size_t n, int kind) {
     unsigned char* d_out = d_in + data;
     unsigned char* d_ws = d_out + data;
     uint64_t* d_counts = reinterpret_cast<uint64_t*>(d_ws + ws_part);
+    unsigned char* ws_sort = d_ws + ws_part + counts_bytes;
+    size_t ws_sort_bytes = ws_sort_cap;
 
     tr.mark("streams + device block ready");
     // the copy-in goes in chunks on the copy stream; while the DMA runs the host picks
-    // the splitters (1-2 ms), then every chunk is histogrammed by destination range on
-    // the compute stream as soon as it has landed: when the last byte arrives only
-    // the scatter of the range split is left to do
-    constexpr int CHUNKS = 16;
-    const size_t per_chunk = ((n + CHUNKS - 1) / CHUNKS + 4095) / 4096 * 4096;  // whole 16-byte vectors for K1
+    // the splitters (1-2 ms), then every chunk is split by destination range (one K7 run
+    // into its own slice of d_out) on the compute stream as soon as it has landed: when
+    // the last byte arrives only the split of the last chunk is left to do
     cudaEvent_t landed[CHUNKS] = {};
     struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < CHUNKS; ++i) if (e[i]) cudaEventDestroy(e[i]); } } eg{landed};
     if (!staged) {
@@ -339,69 +348,81 @@ int keys_host_pipelined(void* host, size_t n, int kind) {
     }
     tr.mark("splitters chosen");
     SortCall pc;
-    pc.elems = d_in; pc.alt_out = d_out; pc.ws = d_ws; pc.ws_bytes = ws_part; pc.n = n; pc.st = cl.s;
+    pc.ws = d_ws; pc.ws_bytes = ws_part; pc.st = cl.s;
     pc.flags = B200SORT_FLAG_NO_SKIP; pc.xf = xf; pc.splitters = spl; pc.nsplit = MAX_SPLITTERS;
-    pc.hist_copy = reinterpret_cast<unsigned long long*>(d_counts); pc.hist_copy_words = PIPE_GROUPS;
-    pc.phase = SortCall::PHASE_COUNT_BEGIN;
-    if ((rc = front_by_width<FAM_PARTITION>(kb, pc))) return rc;
+    pc.hist_copy_words = PIPE_GROUPS;
     size_t bounce_issued = 0;
+    int chunks = 0;
     for (int c = 0; c < CHUNKS; ++c) {
         const size_t off = (size_t)c * per_chunk;
         if (off >= n) break;
         const size_t cnt = std::min(per_chunk, n - off);
-        if (staged) {  // the host thread feeds the bounce buffers; the counts of chunk c run under the copy of chunk c + 1
+        if (staged) {  // the host thread feeds the bounce buffers; the split of chunk c runs under the copy of chunk c + 1
             CU(staged_copy_in(cl.bounce, d_in + off * kb, static_cast<const unsigned char*>(host) + off * kb, cnt * kb, cl.c,
                               &bounce_issued));
             CU(cudaEventCreateWithFlags(&landed[c], cudaEventDisableTiming));
             CU(cudaEventRecord(landed[c], cl.c));
         }
         CU(cudaStreamWaitEvent(cl.s, landed[c], 0));
-        pc.phase = SortCall::PHASE_COUNT_PART; pc.part_off = off; pc.part_n = cnt;
+        pc.elems = d_in + off * kb; pc.alt_out = d_out + off * kb; pc.n = cnt;
+        pc.hist_copy = reinterpret_cast<unsigned long long*>(d_counts) + (size_t)c * PIPE_GROUPS;
         if ((rc = front_by_width<FAM_PARTITION>(kb, pc))) return rc;
+        chunks = c + 1;
     }
-    tr.mark("per-chunk counts enqueued");
+    tr.mark("per-chunk range splits enqueued");
     if (tr.on) { cudaStreamSynchronize(cl.c); tr.mark("copy-in done"); }
-    pc.phase = SortCall::PHASE_COUNT_END;
-    if ((rc = front_by_width<FAM_PARTITION>(kb, pc))) return rc;
-    pc.phase = SortCall::PHASE_SCATTER;
-    if ((rc = front_by_width<FAM_PARTITION>(kb, pc))) return rc;
-    uint64_t counts[PIPE_GROUPS];
-    CU(cudaMemcpyAsync(counts, d_counts, sizeof(counts), cudaMemcpyDeviceToHost, cl.s));
+    uint64_t counts[CHUNKS][PIPE_GROUPS];
+    CU(cudaMemcpyAsync(counts, d_counts, (size_t)chunks * PIPE_GROUPS * 8, cudaMemcpyDeviceToHost, cl.s));
     CU(cudaStreamSynchronize(cl.s));
-    tr.mark("range split done, counts on the host");
+    tr.mark("range splits done, counts on the host");
 
-    // the input buffer is free now: it is the workspace of the range sorts
-    size_t max_g = 0;
-    for (int g = 0; g < PIPE_GROUPS; ++g) max_g = std::max<size_t>(max_g, (size_t)counts[g]);
-    unsigned char* ws_sort = d_in;
-    size_t ws_sort_bytes = data;
+    // range g is now 16 pieces, one per chunk slice of d_out (piece (c, g) starts where the
+    // pieces (c, 0..g-1) end).  The input buffer is free: gather each range there, in range
+    // order, and sort it in place -- the ranges end up contiguous and in order in d_in.
+    size_t total[PIPE_GROUPS] = {}, max_g = 0;
+    for (int g = 0; g < PIPE_GROUPS; ++g) {
+        for (int c = 0; c < chunks; ++c) total[g] += (size_t)counts[c][g];
+        max_g = std::max(max_g, total[g]);
+    }
     const size_t need = b200sort_temp_bytes(max_g, kind);
-    if (need > ws_sort_bytes) {  // heavily skewed keys: one range holds most of them
+    if (need > ws_sort_bytes) {  // skewed keys: one range holds far more than its share
         rc = pool_acquire(need, &cl.extra);
         if (rc) return rc;
         ws_sort = static_cast<unsigned char*>(cl.extra);
         ws_sort_bytes = need;
     }
+    size_t piece_off[CHUNKS] = {};  // start of the next unread piece inside chunk c's slice
     size_t off = 0;
-    for (int g = 0; g < PIPE_GROUPS; ++g) {  // all range sorts first: they are asynchronous
-        const size_t cnt = (size_t)counts[g];
-        if (cnt == 0) continue;
-        rc = keys_device_dispatch(d_out + off * kb, ws_sort, ws_sort_bytes, cnt, kind, cl.s, 0, nullptr, 0);
+    for (int g = 0; g < PIPE_GROUPS; ++g) {  // all gathers + range sorts first: they are asynchronous
+        if (total[g] == 0) continue;
+        size_t at = off;
+        for (int c = 0; c < chunks; ++c) {
+            const size_t cnt = (size_t)counts[c][g];
+            if (cnt == 0) continue;
+            CU(cudaMemcpyAsync(d_in + at * kb, d_out + ((size_t)c * per_chunk + piece_off[c]) * kb, cnt * kb,
+                               cudaMemcpyDeviceToDevice, cl.s));
+            piece_off[c] += cnt;
+            at += cnt;
+        }
+        rc = keys_device_dispatch(d_in + off * kb, ws_sort, ws_sort_bytes, total[g], kind, cl.s, 0, nullptr, 0);
         if (rc) return rc;
         CU(cudaEventCreateWithFlags(&cl.ev[g], cudaEventDisableTiming));
         CU(cudaEventRecord(cl.ev[g], cl.s));
-        off += cnt;
+        if (!staged) {  // pinned slice: the copy-out of a range is queued right behind its sort
+            CU(cudaStreamWaitEvent(cl.c, cl.ev[g], 0));
+            CU(cudaMemcpyAsync(static_cast<unsigned char*>(host) + off * kb, d_in + off * kb, total[g] * kb, cudaMemcpyDeviceToHost, cl.c));
+        }
+        off += total[g];
     }
     if (off != n) return fail(B200SORT_ERR_CUDA, "partition counts do not add up to n");
     tr.mark("range sorts enqueued");
     StagedCopyOut out(cl.bounce, cl.c);
     off = 0;
-    for (int g = 0; g < PIPE_GROUPS; ++g) {  // then the copy-outs, each behind its range's sort
-        const size_t cnt = (size_t)counts[g];
+    for (int g = 0; g < PIPE_GROUPS && staged; ++g) {  // pageable slice: the host thread drains the bounce buffers, range by range
+        const size_t cnt = total[g];
         if (cnt == 0) continue;
         CU(cudaStreamWaitEvent(cl.c, cl.ev[g], 0));
-        if (staged) CU(out.add(static_cast<unsigned char*>(host) + off * kb, d_out + off * kb, cnt * kb));
-        else CU(cudaMemcpyAsync(static_cast<unsigned char*>(host) + off * kb, d_out + off * kb, cnt * kb, cudaMemcpyDeviceToHost, cl.c));
+        CU(out.add(static_cast<unsigned char*>(host) + off * kb, d_in + off * kb, cnt * kb));
         off += cnt;
     }
     if (staged) CU(out.finish());

@@ -75,10 +75,9 @@ int sort_front(const SortCall& c) {
     if (int rc = make_params<FAM, W>(c, &prm)) return rc;
     const int ph = c.phase;
     // (a second scatter over the same counts zeroes the same region: the histogram in it is spent by then)
-    const bool do_zero = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT || ph == SortCall::PHASE_COUNT_BEGIN ||
-                         (ph == SortCall::PHASE_SCATTER && c.rezero);
-    const bool do_hist = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT || ph == SortCall::PHASE_COUNT_PART;
-    const bool do_plan = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT || ph == SortCall::PHASE_COUNT_END;
+    const bool do_hist = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT;
+    const bool do_zero = do_hist || (ph == SortCall::PHASE_SCATTER && c.rezero);
+    const bool do_plan = do_hist;
     const bool do_scatter = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_SCATTER;
     const bool do_count = do_plan;  // the call that delivers the counts
     if (n == 0) {
@@ -140,10 +139,8 @@ int sort_front(const SortCall& c) {
 
     // K1: one read, all digit histograms
     if (do_hist) {
-        const bool part = ph == SortCall::PHASE_COUNT_PART;
-        if (part && c.part_off + c.part_n > n) return fail(B200SORT_ERR_INVALID_ARG, "histogram range outside the keys");
-        const E* h_elems = d_elems + (part ? c.part_off : 0);
-        const size_t h_n = part ? c.part_n : n;
+        const E* h_elems = d_elems;
+        const size_t h_n = n;
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

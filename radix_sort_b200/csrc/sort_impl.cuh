@@ -211,15 +211,10 @@ struct SortCall {
     //   PHASE_COUNT   memset + K1 + K2: leaves histogram, plan and look-back state in ws
     //   PHASE_SCATTER K3 only, on the state PHASE_COUNT left in the same ws; bucket r goes to
     //                 peer_bases[r] (peer memory) starting at element peer_offsets[r]
-    //   PHASE_COUNT_BEGIN / _PART / _END: PHASE_COUNT in pieces -- zero the state, histogram
-    //                 elements [part_off, part_off + part_n) (any number of times), then scan + plan;
-    //                 lets the host path count chunks while later chunks are still being copied in
     //   PHASE_READ_STATS: no kernel; synchronises and copies the workspace's counter of re-ranked tiles to *out_stats
-    enum { PHASE_ALL = 0, PHASE_COUNT = 1, PHASE_SCATTER = 2, PHASE_COUNT_BEGIN = 3, PHASE_COUNT_PART = 4, PHASE_COUNT_END = 5,
-           PHASE_READ_STATS = 6 };
+    enum { PHASE_ALL = 0, PHASE_COUNT = 1, PHASE_SCATTER = 2, PHASE_READ_STATS = 6 };
     unsigned* out_stats = nullptr;
     int phase = PHASE_ALL;
-    size_t part_off = 0, part_n = 0;
     unsigned bucket_mask = 0xFFFFFFFFu;              // PHASE_SCATTER: buckets this launch stores (bit r = bucket r)
     bool rezero = false;                             // PHASE_SCATTER run again on the same state: zero tickets + look-back first
     void* const* peer_bases = nullptr;               // host array, nsplit + 1 device pointers
