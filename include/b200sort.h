@@ -224,6 +224,30 @@ int b200sort_partition_exchange_part_device(const void *d_in, void *d_tmp, size_
                                             const uint64_t *d_peer_offsets, unsigned bucket_mask, int again,
                                             void *stream);
 
+/* ---- all GPUs of one process behind one call --------------------------------
+ * The reference is a single process (`slice.radix_sort()`, mod.rs:18-20,61); a
+ * caller that holds shards on several GPUs of that process sorts them with one
+ * communicator, no launcher and no NCCL: sampled splitters, K7 count, K7
+ * scatter storing every key straight into its destination GPU's receive buffer
+ * over NVLink (peer access is enabled by create), one local sort per GPU.
+ *
+ * b200sort_mgpu_create: ndev in [1, 16]; devs = CUDA device ordinals (NULL =
+ *   0 .. ndev-1).  A device may be named more than once (several shards on one
+ *   GPU).  Fails with B200SORT_ERR_CUDA when two devices have no peer access.
+ * b200sort_mgpu_keys_device: d_shards[r] = n_in[r] keys of `kind` in device
+ *   memory of devs[r]; they are read, not written.  On return d_out[r] points
+ *   to n_out[r] sorted keys on devs[r]: the r-th contiguous range of the global
+ *   order, so that d_out[0] ++ d_out[1] ++ ... is what the reference's sort
+ *   gives for the concatenated input.  The buffers belong to the communicator
+ *   and stay valid until its next sort or its destruction.  Blocking; the
+ *   current device of the calling thread is restored.  One sort at a time per
+ *   communicator (calls are serialised). */
+typedef struct b200sort_comm b200sort_comm;
+int b200sort_mgpu_create(b200sort_comm **comm, int ndev, const int *devs);
+int b200sort_mgpu_keys_device(b200sort_comm *comm, const void *const *d_shards, const size_t *n_in, int kind,
+                              void **d_out, size_t *n_out);
+int b200sort_mgpu_destroy(b200sort_comm *comm);
+
 #ifdef __cplusplus
 }
 #endif

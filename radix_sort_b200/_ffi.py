@@ -44,6 +44,10 @@ PROTOTYPES = {
     "b200sort_debug_reranked_tiles": (c_int, [c_void_p, c_size_t, c_size_t, c_int, c_size_t, c_void_p, POINTER(c_uint)]),
     "b200sort_partition_exchange_part_device": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_int, c_void_p, c_int,
                                                         c_void_p, c_void_p, ctypes.c_uint, c_int, c_void_p]),
+    "b200sort_mgpu_create": (c_int, [POINTER(c_void_p), c_int, POINTER(c_int)]),
+    "b200sort_mgpu_keys_device": (c_int, [c_void_p, POINTER(c_void_p), POINTER(c_size_t), c_int, POINTER(c_void_p),
+                                          POINTER(c_size_t)]),
+    "b200sort_mgpu_destroy": (c_int, [c_void_p]),
 }
 
 _lib = None

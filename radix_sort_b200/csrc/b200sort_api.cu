@@ -636,3 +636,246 @@ int b200sort_num_variants(int key_bytes) {
 }
 
 }  // extern "C"
+
+// ---- all GPUs of one process behind one call (b200sort_mgpu_*) ----------
+// The caller of `slice.radix_sort()` is ONE process; the rank-per-process path
+// (radix_sort_b200/mgpu.py) needs a launcher around it.  This is the same algorithm
+// -- sampled splitters, K7 count, K7 scatter fused with the exchange (every key is
+// stored straight into its destination GPU's receive buffer over NVLink), local
+// sorts -- driven by one host thread over the devices of the communicator.  What
+// the ranks exchange through all_gather there is a host array here, and a barrier
+// is a loop of cudaStreamSynchronize.
+struct b200sort_comm {
+    int ndev = 0;
+    int dev[MAX_SPLITTERS + 1] = {};
+    cudaStream_t st[MAX_SPLITTERS + 1] = {};
+    void* recv[MAX_SPLITTERS + 1] = {};   // receive buffer = result of the device
+    void* part[MAX_SPLITTERS + 1] = {};   // K7 state + counts + offsets + samples
+    void* sortws[MAX_SPLITTERS + 1] = {};  // workspace of the local sort
+    size_t recv_bytes[MAX_SPLITTERS + 1] = {}, part_bytes[MAX_SPLITTERS + 1] = {}, sortws_bytes[MAX_SPLITTERS + 1] = {};
+    std::mutex mu;  // one sort at a time per communicator
+};
+
+namespace {
+
+constexpr size_t MGPU_SAMPLES = (size_t)1 << 14;  // per device, scaled down for smaller shards
+
+struct DeviceGuard {
+    int prev = -1;
+    DeviceGuard() { cudaGetDevice(&prev); }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+template <typename U>
+__global__ void gather_samples_kernel(const U* __restrict__ in, size_t stride, unsigned long long salt, U* __restrict__ out,
+                                      unsigned samples) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < samples) out[i] = in[(size_t)i * stride + (size_t)(mix64(salt ^ mix64(i)) % stride)];
+}
+
+int launch_gather(size_t kb, const void* in, size_t stride, unsigned long long salt, void* out, unsigned samples, cudaStream_t st) {
+    const unsigned blocks = (samples + 255) / 256;
+    switch (kb) {
+    case 1: gather_samples_kernel<<<blocks, 256, 0, st>>>(static_cast<const unsigned char*>(in), stride, salt, static_cast<unsigned char*>(out), samples); break;
+    case 2: gather_samples_kernel<<<blocks, 256, 0, st>>>(static_cast<const unsigned short*>(in), stride, salt, static_cast<unsigned short*>(out), samples); break;
+    case 4: gather_samples_kernel<<<blocks, 256, 0, st>>>(static_cast<const unsigned int*>(in), stride, salt, static_cast<unsigned int*>(out), samples); break;
+    case 8: gather_samples_kernel<<<blocks, 256, 0, st>>>(static_cast<const unsigned long long*>(in), stride, salt, static_cast<unsigned long long*>(out), samples); break;
+    default: gather_samples_kernel<<<blocks, 256, 0, st>>>(static_cast<const u128*>(in), stride, salt, static_cast<u128*>(out), samples); break;
+    }
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaGetLastError());
+    return B200SORT_OK;
+}
+
+// device memory of the communicator grows on demand and is kept between sorts
+int grow(void** p, size_t* have, size_t need) {
+    if (*have >= need && *p) return B200SORT_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr; *have = 0;
+    need = align_up(need + need / 16 + 256, 256);
+    const cudaError_t e = cudaMalloc(p, need);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(B200SORT_ERR_OOM, std::string("cudaMalloc of ") + std::to_string(need) + " bytes: " + cudaGetErrorString(e));
+    }
+    *have = need;
+    return B200SORT_OK;
+}
+
+int sync_all(b200sort_comm* c) {
+    for (int r = 0; r < c->ndev; ++r) {
+        CU(cudaSetDevice(c->dev[r]));
+        CU(cudaStreamSynchronize(c->st[r]));
+    }
+    return B200SORT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200sort_mgpu_create(b200sort_comm** out, int ndev, const int* devs) {
+    if (!out) return fail(B200SORT_ERR_INVALID_ARG, "null communicator pointer");
+    *out = nullptr;
+    if (ndev < 1 || ndev > MAX_SPLITTERS + 1) return fail(B200SORT_ERR_INVALID_ARG, "ndev must be in [1, 16]");
+    int have = 0;
+    CU(cudaGetDeviceCount(&have));
+    DeviceGuard guard;
+    b200sort_comm* c = new b200sort_comm;
+    c->ndev = ndev;
+    for (int r = 0; r < ndev; ++r) {
+        c->dev[r] = devs ? devs[r] : r;
+        if (c->dev[r] < 0 || c->dev[r] >= have) {
+            delete c;
+            return fail(B200SORT_ERR_INVALID_ARG, "no such CUDA device");
+        }
+    }
+    int rc = B200SORT_OK;
+    for (int r = 0; r < ndev && rc == B200SORT_OK; ++r) {
+        cudaError_t e = cudaSetDevice(c->dev[r]);
+        for (int q = 0; q < ndev && e == cudaSuccess; ++q) {  // a device may be named twice (two shards on one GPU)
+            if (c->dev[q] == c->dev[r]) continue;
+            int can = 0;
+            e = cudaDeviceCanAccessPeer(&can, c->dev[r], c->dev[q]);
+            if (e == cudaSuccess && !can) {
+                rc = fail(B200SORT_ERR_CUDA, "no peer access between devices " + std::to_string(c->dev[r]) + " and " + std::to_string(c->dev[q]));
+                break;
+            }
+            if (e == cudaSuccess) {
+                e = cudaDeviceEnablePeerAccess(c->dev[q], 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+            }
+        }
+        if (rc == B200SORT_OK && e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->st[r], cudaStreamNonBlocking);
+        if (rc == B200SORT_OK && e != cudaSuccess) rc = cuda_fail(e, "b200sort_mgpu_create");
+    }
+    if (rc != B200SORT_OK) {
+        b200sort_mgpu_destroy(c);
+        return rc;
+    }
+    *out = c;
+    return B200SORT_OK;
+}
+
+int b200sort_mgpu_destroy(b200sort_comm* c) {
+    if (!c) return B200SORT_OK;
+    DeviceGuard guard;
+    for (int r = 0; r < c->ndev; ++r) {
+        if (cudaSetDevice(c->dev[r]) != cudaSuccess) continue;
+        if (c->st[r]) { cudaStreamSynchronize(c->st[r]); cudaStreamDestroy(c->st[r]); }
+        if (c->recv[r]) cudaFree(c->recv[r]);
+        if (c->part[r]) cudaFree(c->part[r]);
+        if (c->sortws[r]) cudaFree(c->sortws[r]);
+    }
+    cudaGetLastError();
+    delete c;
+    return B200SORT_OK;
+}
+
+int b200sort_mgpu_keys_device(b200sort_comm* c, const void* const* d_shards, const size_t* n_in, int kind,
+                              void** d_out, size_t* n_out) {
+    if (!c || !d_shards || !n_in || !d_out || !n_out) return fail(B200SORT_ERR_INVALID_ARG, "null argument");
+    const size_t kb = b200sort_key_bytes(kind);
+    if (kb == 0) return fail(B200SORT_ERR_UNSUPPORTED_KIND, "unknown key kind " + std::to_string(kind));
+    const int G = c->ndev;
+    const int xf = kind_xf(kind);
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard;
+    Trace tr;
+    int rc;
+    size_t max_n = 0;
+    for (int r = 0; r < G; ++r) {
+        if (n_in[r] && !d_shards[r]) return fail(B200SORT_ERR_INVALID_ARG, "null shard");
+        max_n = std::max(max_n, n_in[r]);
+    }
+    // layout of part[r]: K7 state | counts (G u64) | offsets (G u64) | pooled samples | workspace of their sort
+    // (the last two are used on the first device only)
+    const size_t pool_cap = align_up((size_t)G * MGPU_SAMPLES * 16, 256);
+    const size_t pool_ws = align_up(b200sort_temp_bytes((size_t)G * MGPU_SAMPLES, kind), 256);
+    size_t state_bytes[MAX_SPLITTERS + 1], samples[MAX_SPLITTERS + 1], sample_base[MAX_SPLITTERS + 2] = {0};
+    for (int r = 0; r < G; ++r) {
+        state_bytes[r] = align_up(temp_by_width<FAM_PARTITION>(kb, n_in[r]), 256);
+        // sample count proportional to the shard, so that the pooled quantiles weigh every key alike
+        samples[r] = n_in[r] ? std::max<size_t>(1, std::min(n_in[r], (size_t)((double)MGPU_SAMPLES * (double)n_in[r] / (double)max_n))) : 0;
+        sample_base[r + 1] = sample_base[r] + samples[r];
+        CU(cudaSetDevice(c->dev[r]));
+        if ((rc = grow(&c->part[r], &c->part_bytes[r], state_bytes[r] + 512 + (r == 0 ? pool_cap + pool_ws : 0)))) return rc;
+    }
+    auto counts_of = [&](int r) { return reinterpret_cast<uint64_t*>(static_cast<unsigned char*>(c->part[r]) + state_bytes[r]); };
+    auto offsets_of = [&](int r) { return counts_of(r) + 32; };
+    unsigned char* pool = static_cast<unsigned char*>(c->part[0]) + state_bytes[0] + 512;
+    const size_t pooled = sample_base[G];
+    for (int r = 0; r < G; ++r) { d_out[r] = nullptr; n_out[r] = 0; }
+    if (pooled == 0) return B200SORT_OK;  // nothing to sort
+
+    // 1. splitters: every device stores samples of its shard straight into the first device's
+    //    pool (peer stores); the pool is sorted there with the library's own sort (host
+    //    std::sort of 32 K keys took 1.5 ms) and its quantiles come back to the host
+    for (int r = 0; r < G; ++r) {
+        if (!samples[r]) continue;
+        CU(cudaSetDevice(c->dev[r]));
+        if ((rc = launch_gather(kb, d_shards[r], n_in[r] / samples[r], 0xB200ull + (unsigned long long)r, pool + sample_base[r] * kb,
+                                (unsigned)samples[r], c->st[r])))
+            return rc;
+    }
+    if ((rc = sync_all(c))) return rc;
+    CU(cudaSetDevice(c->dev[0]));
+    if ((rc = keys_device_dispatch(pool, pool + pool_cap, pool_ws, pooled, kind, c->st[0], 0, nullptr, 0))) return rc;
+    alignas(16) unsigned char spl[MAX_SPLITTERS * 16];
+    for (int j = 0; j + 1 < G; ++j)
+        CU(cudaMemcpyAsync(spl + (size_t)j * kb, pool + std::min(pooled - 1, pooled * (size_t)(j + 1) / G) * kb, kb, cudaMemcpyDeviceToHost, c->st[0]));
+    CU(cudaStreamSynchronize(c->st[0]));
+    tr.mark("mgpu: splitters chosen");
+
+    // 2. K7 count on every device; the G x G count matrix comes to the host
+    uint64_t cnt[MAX_SPLITTERS + 1][MAX_SPLITTERS + 1] = {};
+    for (int r = 0; r < G; ++r) {
+        CU(cudaSetDevice(c->dev[r]));
+        if ((rc = partition_phase(SortCall::PHASE_COUNT, d_shards[r], c->part[r], state_bytes[r], n_in[r], kind, spl, G - 1,
+                                  counts_of(r), nullptr, nullptr, c->st[r])))
+            return rc;
+        CU(cudaMemcpyAsync(cnt[r], counts_of(r), (size_t)G * 8, cudaMemcpyDeviceToHost, c->st[r]));
+    }
+    if ((rc = sync_all(c))) return rc;
+    tr.mark("mgpu: counts on the host");
+
+    // 3. receive buffers and the offset at which every sender's keys start in them
+    uint64_t off[MAX_SPLITTERS + 1][MAX_SPLITTERS + 1] = {};
+    size_t total_in = 0, total_out = 0;
+    for (int j = 0; j < G; ++j) {
+        size_t at = 0;
+        for (int r = 0; r < G; ++r) { off[r][j] = at; at += (size_t)cnt[r][j]; }
+        n_out[j] = at;
+        total_out += at;
+        total_in += n_in[j];
+        CU(cudaSetDevice(c->dev[j]));
+        if ((rc = grow(&c->recv[j], &c->recv_bytes[j], at * kb))) return rc;
+        if ((rc = grow(&c->sortws[j], &c->sortws_bytes[j], b200sort_temp_bytes(at, kind)))) return rc;
+    }
+    if (total_in != total_out) return fail(B200SORT_ERR_CUDA, "partition counts do not add up to the input");
+
+    // 4. K7 scatter: every key goes straight to its destination's receive buffer
+    for (int r = 0; r < G; ++r) {
+        if (!n_in[r]) continue;
+        CU(cudaSetDevice(c->dev[r]));
+        CU(cudaMemcpyAsync(offsets_of(r), off[r], (size_t)G * 8, cudaMemcpyHostToDevice, c->st[r]));
+        if ((rc = partition_phase(SortCall::PHASE_SCATTER, d_shards[r], c->part[r], state_bytes[r], n_in[r], kind, spl, G - 1,
+                                  nullptr, c->recv, offsets_of(r), c->st[r])))
+            return rc;
+    }
+    if ((rc = sync_all(c))) return rc;  // every receive buffer is complete
+    tr.mark("mgpu: keys exchanged");
+
+    // 5. local sorts, all devices at once
+    for (int j = 0; j < G; ++j) {
+        d_out[j] = c->recv[j];
+        if (!n_out[j]) continue;
+        CU(cudaSetDevice(c->dev[j]));
+        if ((rc = keys_device_dispatch(c->recv[j], c->sortws[j], c->sortws_bytes[j], n_out[j], kind, c->st[j], 0, nullptr, 0))) return rc;
+    }
+    rc = sync_all(c);
+    tr.mark("mgpu: local sorts done");
+    return rc;
+}
+
+}  // extern "C"

@@ -421,3 +421,79 @@ def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 
     mark("local_sort")
     finish()
     return ShardedResult(typed(recv), n_out, send_counts, recv_counts, splitters)
+
+
+class _DeviceSpan:
+    """`nbytes` bytes of device memory at `ptr`, for torch.as_tensor (CUDA array interface)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+
+class Communicator:
+    """All GPUs of ONE process behind one call: `b200sort_mgpu_create` /
+    `_keys_device` / `_destroy` (include/b200sort.h).  The reference's caller is a
+    single process (`slice.radix_sort()`, mod.rs:18-20,61), so this is the form a
+    shim for it would use when the shards already sit on several GPUs: no launcher,
+    no NCCL -- the exchange is K7 storing into peer memory, the counts travel
+    through the host.
+
+        comm = Communicator([0, 1, 2, 3])
+        outs = comm.sort([shard_on_gpu0, ..., shard_on_gpu3], Kind.U64)
+
+    outs[r] is the r-th contiguous range of the global order, on device r."""
+
+    def __init__(self, devices=None):
+        import torch
+        if devices is None:
+            devices = list(range(torch.cuda.device_count()))
+        self.devices = [int(d) for d in devices]
+        for d in sorted(set(self.devices)):
+            if 0 <= d < torch.cuda.device_count():  # (the library reports the others)
+                torch.zeros(1, device=f"cuda:{d}")  # make sure every device has its primary context
+        arr = (ctypes.c_int * len(self.devices))(*self.devices)
+        self._h = ctypes.c_void_p()
+        check(_ffi.lib().b200sort_mgpu_create(ctypes.byref(self._h), len(self.devices), arr))
+
+    def sort(self, shards, kind, copy: bool = True):
+        """shards[r]: contiguous CUDA tensor on devices[r] ((n, 2) uint64 for 128-bit
+        kinds).  Returns one tensor per device.  copy=False returns views of the
+        communicator's own buffers, valid until its next sort."""
+        import torch
+        k = Kind(kind)
+        kb = NUMBER_OF_DIGITS[k]
+        G = len(self.devices)
+        if len(shards) != G:
+            raise B200SortError(1, f"{G} devices but {len(shards)} shards")
+        for t, d in zip(shards, self.devices):
+            if not (t.is_cuda and t.device.index == d and t.is_contiguous()):
+                raise B200SortError(1, "every shard must be a contiguous tensor on its communicator device")
+            if t.numel() * t.element_size() % kb:
+                raise B200SortError(1, "shard size is not a whole number of keys")
+        torch.cuda.synchronize()  # the library runs on its own streams
+        ptrs = (ctypes.c_void_p * G)(*[t.data_ptr() if t.numel() else None for t in shards])
+        n_in = (ctypes.c_size_t * G)(*[t.numel() * t.element_size() // kb for t in shards])
+        outs = (ctypes.c_void_p * G)()
+        n_out = (ctypes.c_size_t * G)()
+        check(_ffi.lib().b200sort_mgpu_keys_device(self._h, ptrs, n_in, int(k), outs, n_out))
+        res = []
+        for r, (t, d) in enumerate(zip(shards, self.devices)):
+            tail = tuple(t.shape[1:])
+            if n_out[r] == 0:
+                res.append(torch.empty((0,) + tail, dtype=t.dtype, device=t.device))
+                continue
+            raw = torch.as_tensor(_DeviceSpan(int(outs[r]), int(n_out[r]) * kb), device=f"cuda:{d}")
+            view = raw.view(t.dtype).reshape((-1,) + tail)
+            res.append(view.clone() if copy else view)
+        return res
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            _ffi.lib().b200sort_mgpu_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001 -- interpreter shutdown
+            pass

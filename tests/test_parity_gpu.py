@@ -437,6 +437,38 @@ def test_concurrent_host_calls(cuda):
         assert _ref.same_bits(got, want)
 
 
+def test_concurrent_host_calls_pipelined(cuda):
+    """The same, every call forced through the large-slice form (chunk splits, range
+    sorts, shared pinned bounce buffers and copy threads): pageable and pinned slices
+    sorted from four threads at once."""
+    import torch
+    kinds = ["u64", "i32", "f64", "u128"]
+    inputs = [_ref.random_keys(k, 700_000 + 4097 * i, seed=40 + i) for i, k in enumerate(kinds)]
+    outs = [a.copy() for a in inputs]
+    pinned = torch.empty(inputs[0].nbytes, dtype=torch.uint8, pin_memory=True)  # thread 0 sorts a pinned slice
+    outs[0] = pinned.numpy().view(inputs[0].dtype)
+    errs = []
+
+    def work(i):
+        try:
+            for _ in range(3):
+                outs[i][...] = inputs[i]
+                rs.radix_sort(outs[i], _kind(kinds[i]))
+        except Exception as exc:  # noqa: BLE001
+            errs.append(exc)
+
+    rs.set_host_pipeline_min_bytes(0)
+    try:
+        th = [threading.Thread(target=work, args=(i,)) for i in range(len(kinds))]
+        [t.start() for t in th]
+        [t.join() for t in th]
+    finally:
+        rs.set_host_pipeline_min_bytes(64 << 20)
+    assert not errs, errs
+    for k, a, got in zip(kinds, inputs, outs):
+        assert _ref.same_bits(got, _ref.expected_sorted(a, k))
+
+
 def test_cuda_graph_capture_of_device_sort(cuda):
     import torch
     n = 1_000_000
@@ -639,3 +671,91 @@ def test_portion_boundary_small_keys(cuda):
     got = t[torch.from_numpy(np.minimum(bounds - 1, n - 1)).to(cuda)].cpu().numpy()
     present = counts.cpu().numpy() > 0
     assert (got[present] == np.arange(256)[present]).all()
+
+
+# ---- all GPUs of one process behind one call (b200sort_mgpu_*) -------------------
+def _check_communicator(comm, shards_np, kind):
+    import torch
+    from radix_sort_b200 import mgpu
+    shards = [torch.from_numpy(a).to(f"cuda:{d}") for a, d in zip(shards_np, comm.devices)]
+    outs = comm.sort(shards, _kind(kind))
+    for t, a in zip(shards, shards_np):  # inputs are read, not written
+        assert _ref.same_bits(t.cpu().numpy(), a)
+    got = [o.cpu().numpy() for o in outs]
+    for o, d in zip(outs, comm.devices):
+        assert o.device.index == d
+    whole = np.concatenate(shards_np)
+    want = whole.copy()
+    cpu_oracle.sort0(want, kind)
+    assert _ref.same_bits(np.concatenate(got), want)  # rank order = global order
+    return [len(g) for g in got]
+
+
+@pytest.mark.parametrize("kind", ["u32", "u64", "i64", "f32", "f64", "u128", "i8", "u16"])
+def test_communicator_shards_on_one_device(kind, cuda):
+    """Three shards of one process sorted as one key set (the same device named three
+    times: the count / offset / scatter / local-sort logic without needing three GPUs)."""
+    from radix_sort_b200 import mgpu
+    comm = mgpu.Communicator([0, 0, 0])
+    try:
+        sizes = _check_communicator(comm, [_ref.random_keys(kind, n, seed=70 + i) for i, n in enumerate((200_003, 150_000, 99_999))], kind)
+        if kind not in ("i8", "u16"):  # few distinct values: whole values land on one shard
+            assert max(sizes) < 1.2 * sum(sizes) / 3
+        # ragged: an empty shard, a one-key shard; buffers of the first sort are reused
+        _check_communicator(comm, [_ref.random_keys(kind, n, seed=80 + i) for i, n in enumerate((0, 1, 50_000))], kind)
+        # all keys equal: everything lands on one shard
+        same = _ref.random_keys(kind, 30_000, seed=3)
+        same[:] = same[0]
+        sizes = _check_communicator(comm, [same[:10_000].copy(), same[10_000:20_000].copy(), same[20_000:].copy()], kind)
+        assert sorted(sizes) == [0, 0, 30_000]
+        # nothing at all
+        empty = _ref.random_keys(kind, 0, seed=1)
+        assert _check_communicator(comm, [empty, empty.copy(), empty.copy()], kind) == [0, 0, 0]
+    finally:
+        comm.close()
+
+
+def test_communicator_single_device_and_floats(cuda):
+    from radix_sort_b200 import mgpu
+    comm = mgpu.Communicator([0])
+    try:
+        _check_communicator(comm, [_ref.random_keys("u64", 300_001, seed=9)], "u64")
+        _check_communicator(comm, [_ref.float_test_keys("f32", 100_000, seed=4)], "f32")
+    finally:
+        comm.close()
+    comm = mgpu.Communicator([0, 0])
+    try:
+        a = _ref.float_test_keys("f64", 120_000, seed=6)  # specials: +-0, +-inf, NaNs of both signs
+        _check_communicator(comm, [a[:50_000].copy(), a[50_000:].copy()], "f64")
+    finally:
+        comm.close()
+
+
+def test_communicator_rejects_bad_arguments(cuda):
+    import torch
+    from radix_sort_b200 import mgpu
+    with pytest.raises(rs.B200SortError):
+        mgpu.Communicator([0] * 17)
+    with pytest.raises(rs.B200SortError):
+        mgpu.Communicator([torch.cuda.device_count() + 3])
+    comm = mgpu.Communicator([0, 0])
+    try:
+        with pytest.raises(rs.B200SortError):
+            comm.sort([torch.zeros(4, dtype=torch.int32, device=cuda)], rs.Kind.I32)  # one shard for two devices
+    finally:
+        comm.close()
+
+
+def test_communicator_all_visible_devices(cuda):
+    """One shard per GPU of the box, every key crossing NVLink to its owner (needs >= 2 GPUs)."""
+    import torch
+    from radix_sort_b200 import mgpu
+    g = torch.cuda.device_count()
+    if g < 2:
+        pytest.skip("one GPU visible")
+    comm = mgpu.Communicator(list(range(g)))
+    try:
+        for kind in ("u64", "f32", "u128"):
+            _check_communicator(comm, [_ref.random_keys(kind, 400_000 + 4099 * r, seed=90 + r) for r in range(g)], kind)
+    finally:
+        comm.close()
