@@ -247,6 +247,15 @@ int b200sort_mgpu_create(b200sort_comm **comm, int ndev, const int *devs);
 int b200sort_mgpu_keys_device(b200sort_comm *comm, const void *const *d_shards, const size_t *n_in, int kind,
                               void **d_out, size_t *n_out);
 int b200sort_mgpu_destroy(b200sort_comm *comm);
+/* The drop-in call on all devices of the communicator: `keys` is a HOST slice
+ * of n keys (what `slice.radix_sort()` is called on, mod.rs:18-20), sorted in
+ * place.  Device r copies the r-th n/ndev keys in over its own PCIe link, the
+ * parts are sorted as one key set (b200sort_mgpu_keys_device), and device r
+ * copies its range of the result back to its place in the slice.  Slices
+ * below 32 MiB (b200sort_mgpu_set_host_min_bytes) and one-device communicators
+ * go to b200sort_keys_host on the first device.  Blocking. */
+int b200sort_mgpu_keys_host(b200sort_comm *comm, void *keys, size_t n, int kind);
+int b200sort_mgpu_set_host_min_bytes(size_t bytes);
 
 #ifdef __cplusplus
 }

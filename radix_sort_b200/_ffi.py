@@ -48,6 +48,8 @@ PROTOTYPES = {
     "b200sort_mgpu_keys_device": (c_int, [c_void_p, POINTER(c_void_p), POINTER(c_size_t), c_int, POINTER(c_void_p),
                                           POINTER(c_size_t)]),
     "b200sort_mgpu_destroy": (c_int, [c_void_p]),
+    "b200sort_mgpu_keys_host": (c_int, [c_void_p, c_void_p, c_size_t, c_int]),
+    "b200sort_mgpu_set_host_min_bytes": (c_int, [c_size_t]),
 }
 
 _lib = None

@@ -14,6 +14,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "sort_impl.cuh"
@@ -652,13 +653,16 @@ struct b200sort_comm {
     void* recv[MAX_SPLITTERS + 1] = {};   // receive buffer = result of the device
     void* part[MAX_SPLITTERS + 1] = {};   // K7 state + counts + offsets + samples
     void* sortws[MAX_SPLITTERS + 1] = {};  // workspace of the local sort
-    size_t recv_bytes[MAX_SPLITTERS + 1] = {}, part_bytes[MAX_SPLITTERS + 1] = {}, sortws_bytes[MAX_SPLITTERS + 1] = {};
+    void* in[MAX_SPLITTERS + 1] = {};      // b200sort_mgpu_keys_host: the device's part of the host slice
+    size_t recv_bytes[MAX_SPLITTERS + 1] = {}, part_bytes[MAX_SPLITTERS + 1] = {}, sortws_bytes[MAX_SPLITTERS + 1] = {},
+           in_bytes[MAX_SPLITTERS + 1] = {};
     std::mutex mu;  // one sort at a time per communicator
 };
 
 namespace {
 
 constexpr size_t MGPU_SAMPLES = (size_t)1 << 14;  // per device, scaled down for smaller shards
+std::atomic<size_t> g_mgpu_host_min_bytes{(size_t)32 << 20};  // smaller host slices stay on the first device
 
 struct DeviceGuard {
     int prev = -1;
@@ -766,21 +770,18 @@ int b200sort_mgpu_destroy(b200sort_comm* c) {
         if (c->recv[r]) cudaFree(c->recv[r]);
         if (c->part[r]) cudaFree(c->part[r]);
         if (c->sortws[r]) cudaFree(c->sortws[r]);
+        if (c->in[r]) cudaFree(c->in[r]);
     }
     cudaGetLastError();
     delete c;
     return B200SORT_OK;
 }
 
-int b200sort_mgpu_keys_device(b200sort_comm* c, const void* const* d_shards, const size_t* n_in, int kind,
-                              void** d_out, size_t* n_out) {
-    if (!c || !d_shards || !n_in || !d_out || !n_out) return fail(B200SORT_ERR_INVALID_ARG, "null argument");
+// the sort proper; the caller holds c->mu and restores the current device
+static int mgpu_sort_locked(b200sort_comm* c, const void* const* d_shards, const size_t* n_in, int kind, void** d_out,
+                            size_t* n_out) {
     const size_t kb = b200sort_key_bytes(kind);
-    if (kb == 0) return fail(B200SORT_ERR_UNSUPPORTED_KIND, "unknown key kind " + std::to_string(kind));
     const int G = c->ndev;
-    const int xf = kind_xf(kind);
-    std::lock_guard<std::mutex> lk(c->mu);
-    DeviceGuard guard;
     Trace tr;
     int rc;
     size_t max_n = 0;
@@ -876,6 +877,81 @@ int b200sort_mgpu_keys_device(b200sort_comm* c, const void* const* d_shards, con
     rc = sync_all(c);
     tr.mark("mgpu: local sorts done");
     return rc;
+}
+
+int b200sort_mgpu_keys_device(b200sort_comm* c, const void* const* d_shards, const size_t* n_in, int kind,
+                              void** d_out, size_t* n_out) {
+    if (!c || !d_shards || !n_in || !d_out || !n_out) return fail(B200SORT_ERR_INVALID_ARG, "null argument");
+    if (b200sort_key_bytes(kind) == 0) return fail(B200SORT_ERR_UNSUPPORTED_KIND, "unknown key kind " + std::to_string(kind));
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard guard;
+    return mgpu_sort_locked(c, d_shards, n_in, kind, d_out, n_out);
+}
+
+// one host slice over all devices of the communicator: every device copies its part
+// in over its own PCIe link, the parts are sorted as one key set, every device copies
+// its range of the result back to where it belongs in the slice
+int b200sort_mgpu_keys_host(b200sort_comm* c, void* keys, size_t n, int kind) {
+    if (!c) return fail(B200SORT_ERR_INVALID_ARG, "null communicator");
+    const size_t kb = b200sort_key_bytes(kind);
+    if (kb == 0) return fail(B200SORT_ERR_UNSUPPORTED_KIND, "unknown key kind " + std::to_string(kind));
+    if (n == 0) return B200SORT_OK;
+    if (!keys) return fail(B200SORT_ERR_INVALID_ARG, "null keys");
+    const int G = c->ndev;
+    DeviceGuard guard;
+    if (G == 1 || n * kb < g_mgpu_host_min_bytes.load(std::memory_order_relaxed)) {  // not worth an exchange
+        CU(cudaSetDevice(c->dev[0]));
+        return b200sort_keys_host(keys, n, kind);
+    }
+    std::lock_guard<std::mutex> lk(c->mu);
+    Trace tr;
+    int rc;
+    unsigned char* host = static_cast<unsigned char*>(keys);
+    size_t n_in[MAX_SPLITTERS + 1] = {}, n_out[MAX_SPLITTERS + 1] = {}, at[MAX_SPLITTERS + 2] = {0};
+    void* d_out[MAX_SPLITTERS + 1] = {};
+    const size_t per = (n + G - 1) / G;
+    for (int r = 0; r < G; ++r) {
+        const size_t lo = std::min(n, (size_t)r * per);
+        n_in[r] = std::min(per, n - lo);
+        at[r + 1] = lo + n_in[r];
+        CU(cudaSetDevice(c->dev[r]));
+        if ((rc = grow(&c->in[r], &c->in_bytes[r], n_in[r] * kb))) return rc;
+    }
+    // one host thread per device for the copies: DMAs of pinned memory run side by side
+    // anyway, and for a pageable slice (a plain Vec<T>) the driver's staging copy is
+    // single-threaded per call, so G calls at once is what fills G links
+    auto copy_all = [&](bool in_dir, const size_t* offs, const size_t* counts) -> int {
+        cudaError_t err[MAX_SPLITTERS + 1] = {};
+        std::vector<std::thread> th;
+        for (int r = 0; r < G; ++r)
+            th.emplace_back([&, r] {
+                if (!counts[r]) return;
+                cudaError_t e = cudaSetDevice(c->dev[r]);
+                if (e == cudaSuccess)
+                    e = in_dir ? cudaMemcpyAsync(c->in[r], host + offs[r] * kb, counts[r] * kb, cudaMemcpyHostToDevice, c->st[r])
+                               : cudaMemcpyAsync(host + offs[r] * kb, c->recv[r], counts[r] * kb, cudaMemcpyDeviceToHost, c->st[r]);
+                if (e == cudaSuccess) e = cudaStreamSynchronize(c->st[r]);
+                err[r] = e;
+            });
+        for (auto& t : th) t.join();
+        for (int r = 0; r < G; ++r)
+            if (err[r] != cudaSuccess) return cuda_fail(err[r], in_dir ? "copy-in of a device's part" : "copy-out of a device's range");
+        return B200SORT_OK;
+    };
+    if ((rc = copy_all(true, at, n_in))) return rc;
+    tr.mark("mgpu host: parts copied in");
+    if ((rc = mgpu_sort_locked(c, c->in, n_in, kind, d_out, n_out))) return rc;
+    size_t out_at[MAX_SPLITTERS + 2] = {0};
+    for (int r = 0; r < G; ++r) out_at[r + 1] = out_at[r] + n_out[r];
+    if (out_at[G] != n) return fail(B200SORT_ERR_CUDA, "ranges do not add up to n");
+    rc = copy_all(false, out_at, n_out);
+    tr.mark("mgpu host: ranges copied out");
+    return rc;
+}
+
+int b200sort_mgpu_set_host_min_bytes(size_t bytes) {
+    g_mgpu_host_min_bytes.store(bytes, std::memory_order_relaxed);
+    return B200SORT_OK;
 }
 
 }  // extern "C"

@@ -487,6 +487,17 @@ class Communicator:
             res.append(view.clone() if copy else view)
         return res
 
+    def sort_host(self, keys, kind) -> None:
+        """`keys`: a C-contiguous writable numpy array in HOST memory, sorted in place by
+        all devices of the communicator (`b200sort_mgpu_keys_host`): the drop-in call
+        for `slice.radix_sort()` on a box with several GPUs."""
+        k = Kind(kind)
+        if not (isinstance(keys, np.ndarray) and keys.flags["C_CONTIGUOUS"] and keys.flags["WRITEABLE"]):
+            raise B200SortError(1, "keys must be a C-contiguous writable numpy array")
+        if keys.nbytes % NUMBER_OF_DIGITS[k]:
+            raise B200SortError(1, "array size is not a whole number of keys")
+        check(_ffi.lib().b200sort_mgpu_keys_host(self._h, keys.ctypes.data, keys.nbytes // NUMBER_OF_DIGITS[k], int(k)))
+
     def close(self):
         if getattr(self, "_h", None) is not None and self._h:
             _ffi.lib().b200sort_mgpu_destroy(self._h)
