@@ -251,9 +251,10 @@ int b200sort_mgpu_destroy(b200sort_comm *comm);
  * of n keys (what `slice.radix_sort()` is called on, mod.rs:18-20), sorted in
  * place.  Device r copies the r-th n/ndev keys in over its own PCIe link, the
  * parts are sorted as one key set (b200sort_mgpu_keys_device), and device r
- * copies its range of the result back to its place in the slice.  Slices
- * below 32 MiB (b200sort_mgpu_set_host_min_bytes) and one-device communicators
- * go to b200sort_keys_host on the first device.  Blocking. */
+ * copies its range of the result back to its place in the slice.  That is the
+ * route of a PINNED slice (cudaHostRegister / cudaHostAlloc); a pageable one,
+ * slices below 32 MiB (b200sort_mgpu_set_host_min_bytes) and one-device
+ * communicators go to b200sort_keys_host on the first device.  Blocking. */
 int b200sort_mgpu_keys_host(b200sort_comm *comm, void *keys, size_t n, int kind);
 int b200sort_mgpu_set_host_min_bytes(size_t bytes);
 

@@ -899,7 +899,11 @@ int b200sort_mgpu_keys_host(b200sort_comm* c, void* keys, size_t n, int kind) {
     if (!keys) return fail(B200SORT_ERR_INVALID_ARG, "null keys");
     const int G = c->ndev;
     DeviceGuard guard;
-    if (G == 1 || n * kb < g_mgpu_host_min_bytes.load(std::memory_order_relaxed)) {  // not worth an exchange
+    // a pageable slice (a plain Vec<T>) moves at the speed of the host-side staging copy
+    // (host_staging.cuh), and the driver's own staging, which G plain copies would use, is
+    // far slower still (2 GPUs, 1 B u64: 733 ms against 310 on one device): it stays on the
+    // first device until the bounce buffers are per device
+    if (G == 1 || n * kb < g_mgpu_host_min_bytes.load(std::memory_order_relaxed) || is_pageable(keys)) {
         CU(cudaSetDevice(c->dev[0]));
         return b200sort_keys_host(keys, n, kind);
     }
@@ -917,9 +921,7 @@ int b200sort_mgpu_keys_host(b200sort_comm* c, void* keys, size_t n, int kind) {
         CU(cudaSetDevice(c->dev[r]));
         if ((rc = grow(&c->in[r], &c->in_bytes[r], n_in[r] * kb))) return rc;
     }
-    // one host thread per device for the copies: DMAs of pinned memory run side by side
-    // anyway, and for a pageable slice (a plain Vec<T>) the driver's staging copy is
-    // single-threaded per call, so G calls at once is what fills G links
+    // one host thread per device for the copies (the DMAs of a pinned slice run side by side)
     auto copy_all = [&](bool in_dir, const size_t* offs, const size_t* counts) -> int {
         cudaError_t err[MAX_SPLITTERS + 1] = {};
         std::vector<std::thread> th;

@@ -763,31 +763,36 @@ def test_communicator_all_visible_devices(cuda):
 
 @pytest.mark.parametrize("kind", ["u64", "i32", "f64", "u128", "u8"])
 def test_communicator_host_slice(kind, cuda):
-    """b200sort_mgpu_keys_host: one host slice, every device takes a part (the same GPU
-    named three times here), result in place and bit-identical to the oracle."""
+    """b200sort_mgpu_keys_host: one pinned host slice, every device takes a part (the same
+    GPU named three times here), result in place and bit-identical to the oracle."""
+    import torch
     from radix_sort_b200 import mgpu
+
+    def pinned_copy(a):
+        buf = torch.empty(max(a.nbytes, 1), dtype=torch.uint8, pin_memory=True)
+        view = buf.numpy()[: a.nbytes].view(a.dtype).reshape(a.shape)
+        view[...] = a
+        return buf, view
+
     comm = mgpu.Communicator([0, 0, 0])
     L = _ffi.lib()
     L.b200sort_mgpu_set_host_min_bytes(0)
     try:
         for n in (1, 2, 5, 100_003, 600_000):
             a = _ref.random_keys(kind, n, seed=n + 17)
-            got = a.copy()
+            keep, got = pinned_copy(a)
             comm.sort_host(got, _kind(kind))
             want = a.copy()
             cpu_oracle.sort0(want, kind)
             assert _ref.same_bits(got, want)
         comm.sort_host(_ref.random_keys(kind, 0, seed=1), _kind(kind))  # empty slice: returns
-        import torch
-        a = _ref.random_keys(kind, 250_000, seed=5)  # a pinned slice
-        pinned = torch.empty(a.nbytes, dtype=torch.uint8, pin_memory=True)
-        view = pinned.numpy().view(a.dtype).reshape(a.shape)
-        view[...] = a
-        comm.sort_host(view, _kind(kind))
-        assert _ref.same_bits(view, _ref.expected_sorted(a, kind))
-        # below the threshold the call is b200sort_keys_host on the first device
-        L.b200sort_mgpu_set_host_min_bytes(32 << 20)
+        # a pageable slice, and any slice below the threshold, is b200sort_keys_host on the first device
+        a = _ref.random_keys(kind, 250_000, seed=5)
         got = a.copy()
+        comm.sort_host(got, _kind(kind))
+        assert _ref.same_bits(got, _ref.expected_sorted(a, kind))
+        L.b200sort_mgpu_set_host_min_bytes(32 << 20)
+        keep, got = pinned_copy(a)
         comm.sort_host(got, _kind(kind))
         assert _ref.same_bits(got, _ref.expected_sorted(a, kind))
     finally:

@@ -20,7 +20,10 @@ distr.generate(src, K, distr.Distr.UNIFORM, 0, seed=0xB2000002)
 pinned = torch.empty(n, dtype=torch.uint64, pin_memory=True)
 comm = mgpu.Communicator(list(range(g)))
 out = {"what": "b200sort_mgpu_keys_host, one process", "n_gpus": g, "n": n, "kind": "u64"}
-for name, buf in (("pinned", pinned.numpy()), ("pageable", np.empty(n, dtype=np.uint64))):
+legs = [("pinned", pinned.numpy())]
+if "pageable" in sys.argv[2:]:
+    legs.append(("pageable", np.empty(n, dtype=np.uint64)))
+for name, buf in legs:
     best = 1e9
     for i in range(3):
         buf[...] = src.cpu().numpy() if name == "pageable" else 0
