@@ -153,6 +153,7 @@ struct Bounce {
     static constexpr size_t BUF = (size_t)16 << 20;
     unsigned char* base = nullptr;  // NBUF * BUF bytes of pinned memory
     cudaEvent_t done[NBUF] = {};    // DMA that last used buffer i
+    int dev = -1;                   // device the events belong to (an event is recorded on streams of its own device only)
     unsigned char* buf(int i) const { return base + (size_t)i * BUF; }
 };
 
@@ -165,16 +166,22 @@ inline std::vector<Bounce>& bounce_free() {
     return v;
 }
 inline cudaError_t bounce_acquire(Bounce* out) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
     {
         std::lock_guard<std::mutex> lk(bounce_mu());
-        if (!bounce_free().empty()) {
-            *out = bounce_free().back();
-            bounce_free().pop_back();
-            return cudaSuccess;
-        }
+        auto& free_list = bounce_free();
+        for (size_t i = free_list.size(); i-- > 0;)
+            if (free_list[i].dev == dev) {
+                *out = free_list[i];
+                free_list.erase(free_list.begin() + (long)i);
+                return cudaSuccess;
+            }
     }
     Bounce b;
-    cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&b.base), Bounce::NBUF * Bounce::BUF, cudaHostAllocDefault);
+    b.dev = dev;
+    e = cudaHostAlloc(reinterpret_cast<void**>(&b.base), Bounce::NBUF * Bounce::BUF, cudaHostAllocPortable);
     if (e != cudaSuccess) return e;
     for (int i = 0; i < Bounce::NBUF; ++i) {
         e = cudaEventCreateWithFlags(&b.done[i], cudaEventDisableTiming);

@@ -798,3 +798,25 @@ def test_communicator_host_slice(kind, cuda):
     finally:
         L.b200sort_mgpu_set_host_min_bytes(32 << 20)
         comm.close()
+
+
+def test_host_path_on_every_device(cuda):
+    """b200sort_keys_host runs on the calling thread's current device: pooled blocks,
+    cached streams and pinned bounce buffers (with their events) are per device
+    (needs >= 2 GPUs)."""
+    import torch
+    g = torch.cuda.device_count()
+    if g < 2:
+        pytest.skip("one GPU visible")
+    rs.set_host_pipeline_min_bytes(0)  # the pipelined form stages a pageable slice at any size
+    try:
+        for d in list(range(g)) + [0]:
+            with torch.cuda.device(d):
+                for kind in ("u64", "f32"):
+                    _check_host(_ref.random_keys(kind, 300_000 + d, seed=d), kind)
+        rs.set_host_pipeline_min_bytes(64 << 20)
+        for d in range(g):
+            with torch.cuda.device(d):
+                _check_host(_ref.random_keys("i64", 200_000 + d, seed=d), "i64")
+    finally:
+        rs.set_host_pipeline_min_bytes(64 << 20)
