@@ -656,6 +656,8 @@ struct b200sort_comm {
     void* in[MAX_SPLITTERS + 1] = {};      // b200sort_mgpu_keys_host: the device's part of the host slice
     size_t recv_bytes[MAX_SPLITTERS + 1] = {}, part_bytes[MAX_SPLITTERS + 1] = {}, sortws_bytes[MAX_SPLITTERS + 1] = {},
            in_bytes[MAX_SPLITTERS + 1] = {};
+    uint64_t* h_counts = nullptr;  // pinned: a device->host copy into pageable memory blocks the host until it is done,
+                                   // which would run the devices' count phases one after the other
     std::mutex mu;  // one sort at a time per communicator
 };
 
@@ -753,6 +755,11 @@ int b200sort_mgpu_create(b200sort_comm** out, int ndev, const int* devs) {
         if (rc == B200SORT_OK && e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->st[r], cudaStreamNonBlocking);
         if (rc == B200SORT_OK && e != cudaSuccess) rc = cuda_fail(e, "b200sort_mgpu_create");
     }
+    if (rc == B200SORT_OK) {
+        const cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&c->h_counts),
+                                            sizeof(uint64_t) * (MAX_SPLITTERS + 1) * (MAX_SPLITTERS + 1), cudaHostAllocPortable);
+        if (e != cudaSuccess) rc = cuda_fail(e, "cudaHostAlloc(count matrix)");
+    }
     if (rc != B200SORT_OK) {
         b200sort_mgpu_destroy(c);
         return rc;
@@ -772,6 +779,7 @@ int b200sort_mgpu_destroy(b200sort_comm* c) {
         if (c->sortws[r]) cudaFree(c->sortws[r]);
         if (c->in[r]) cudaFree(c->in[r]);
     }
+    if (c->h_counts) cudaFreeHost(c->h_counts);
     cudaGetLastError();
     delete c;
     return B200SORT_OK;
@@ -835,9 +843,11 @@ static int mgpu_sort_locked(b200sort_comm* c, const void* const* d_shards, const
         if ((rc = partition_phase(SortCall::PHASE_COUNT, d_shards[r], c->part[r], state_bytes[r], n_in[r], kind, spl, G - 1,
                                   counts_of(r), nullptr, nullptr, c->st[r])))
             return rc;
-        CU(cudaMemcpyAsync(cnt[r], counts_of(r), (size_t)G * 8, cudaMemcpyDeviceToHost, c->st[r]));
+        CU(cudaMemcpyAsync(c->h_counts + (size_t)r * (MAX_SPLITTERS + 1), counts_of(r), (size_t)G * 8, cudaMemcpyDeviceToHost, c->st[r]));
     }
     if ((rc = sync_all(c))) return rc;
+    for (int r = 0; r < G; ++r)
+        for (int j = 0; j < G; ++j) cnt[r][j] = c->h_counts[(size_t)r * (MAX_SPLITTERS + 1) + j];
     tr.mark("mgpu: counts on the host");
 
     // 3. receive buffers and the offset at which every sender's keys start in them
