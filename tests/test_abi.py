@@ -101,3 +101,51 @@ def test_product_never_imports_the_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 for pat in (r"^\s*(from|import)\s+oracle", r"liboracle", r"oracle[/\\.]", r"cpu_oracle"):
                     assert not re.search(pat, text, flags=re.M), f"{f} reaches into oracle/ ({pat})"
+
+
+_C_CALLER = r"""
+#include <stdio.h>
+#include <string.h>
+#include "b200sort.h"
+
+/* what a C (or cgo / Rust `extern "C"`) caller sees: plain pointers and sizes.
+ * Only calls that are answered before any CUDA work. */
+int main(void) {
+    b200sort_comm *comm = (b200sort_comm *)0;
+    if (b200sort_version() != B200SORT_VERSION) return 1;
+    if (b200sort_key_bytes(B200SORT_U64) != 8 || b200sort_key_bytes(B200SORT_I128) != 16) return 2;
+    if (b200sort_key_bytes(B200SORT_KIND_COUNT) != 0) return 3;
+    if (b200sort_temp_bytes(1000, B200SORT_F32) < 4000) return 4;
+    if (b200sort_keys_host((void *)0, 0, B200SORT_U32) != B200SORT_OK) return 5;          /* empty slice */
+    if (b200sort_keys_host((void *)0, 0, 99) != B200SORT_ERR_UNSUPPORTED_KIND) return 6;
+    if (strlen(b200sort_last_error()) == 0) return 7;
+    if (b200sort_mgpu_create(&comm, 0, (const int *)0) != B200SORT_ERR_INVALID_ARG || comm) return 8;
+    if (b200sort_mgpu_create(&comm, 17, (const int *)0) != B200SORT_ERR_INVALID_ARG || comm) return 9;
+    if (b200sort_mgpu_keys_host((b200sort_comm *)0, (void *)0, 0, B200SORT_U8) != B200SORT_ERR_INVALID_ARG) return 10;
+    if (b200sort_mgpu_destroy((b200sort_comm *)0) != B200SORT_OK) return 11;
+    puts("ok");
+    return 0;
+}
+"""
+
+
+def test_header_is_plain_c_and_a_c_program_links(tmp_path):
+    """include/b200sort.h compiles as C99 with -pedantic -Werror, and a C program
+    linked against libb200sort.so gets the documented answers (no GPU needed)."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    lib = _build.build()
+    src = tmp_path / "caller.c"
+    src.write_text(_C_CALLER)
+    exe = tmp_path / "caller"
+    inc = os.path.join(ROOT, "include")
+    subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", "-fsyntax-only", "-x", "c",
+                    os.path.join(inc, "b200sort.h")], check=True)
+    libdir = os.path.dirname(lib)
+    subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", "-I", inc, str(src), "-o", str(exe),
+                    "-L", libdir, "-lb200sort", f"-Wl,-rpath,{libdir}"], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0, f"check {out.returncode} failed: {out.stderr}"
+    assert out.stdout.strip() == "ok"
