@@ -68,6 +68,13 @@ def test_harness_notices_a_sort_that_does_not_sort(tmp_path):
     assert "radix_sort_tuple ... FAILED (b200sort error 3: lazy)" in out.stdout  # a non-zero status is the panic
 
 
+def test_mirror_compile_time_facts():
+    """NUMBER_OF_DIGITS and kind of every built-in impl (radix_digits.rs:7-136); types
+    without a get_digit have no RadixDigits (static_asserts: compiling is the test)."""
+    subprocess.run(["g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-I", INC, "-fsyntax-only",
+                    os.path.join(CPP, "mirror_static.cpp")], check=True)
+
+
 def test_mirror_links_against_the_library(tmp_path):
     lib = _build.build()
     obj = _compile_harness(str(tmp_path))
