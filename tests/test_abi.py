@@ -93,6 +93,19 @@ def test_no_cpu_fallback_without_a_device():
     assert a.tolist() == [3, 1, 2]  # untouched: nothing sorted it on the CPU
 
 
+def test_communicator_fails_loudly_without_a_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    from radix_sort_b200 import mgpu
+    with pytest.raises(rs.B200SortError) as e:
+        mgpu.Communicator([0])
+    assert e.value.code == 3
+    with pytest.raises(rs.B200SortError) as e:  # argument errors are answered before any CUDA call
+        mgpu.Communicator([0] * 17)
+    assert e.value.code == 1
+
+
 def test_product_never_imports_the_oracle():
     pkg = os.path.join(ROOT, "radix_sort_b200")
     for dirpath, _, files in os.walk(pkg):
