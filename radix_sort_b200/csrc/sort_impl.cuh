@@ -62,10 +62,13 @@ template <int FAM, int W> struct Variants;
 template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}, {3, 512, 32, 2, 0}}; };
 #define B200_NV_KEYS_2 2
 template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}, {3, 512, 24, 2, 0}}; };
-#define B200_NV_KEYS_4 4
-template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 26, 2, 0}, {3, 512, 22, 2, 0}, {0, 512, 22, 2, 0}, {0, 512, 16, 2, 0}}; };
-#define B200_NV_KEYS_8 3
-template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {3, 512, 16, 2, 0}, {0, 256, 20, 3, 0}}; };
+// (lbb bits 8+: FEAT_STG = 32 -> 0x2000, FEAT_NODOM = 64 -> 0x4000)
+#define B200_NV_KEYS_4 9
+template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 26, 2, 0}, {3, 512, 22, 2, 0}, {0, 512, 22, 2, 0}, {0, 512, 16, 2, 0},
+    {0, 512, 26, 2, 0x2000}, {0, 512, 26, 2, 0x4000}, {0, 512, 26, 2, 0x6000}, {0, 1024, 26, 1, 0x6000}, {0, 1024, 20, 1, 0x6000}}; };
+#define B200_NV_KEYS_8 8
+template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {3, 512, 16, 2, 0}, {0, 256, 20, 3, 0},
+    {0, 512, 16, 2, 0x2000}, {0, 512, 16, 2, 0x4000}, {0, 512, 16, 2, 0x6000}, {0, 1024, 16, 1, 0x6000}, {0, 1024, 12, 1, 0x6000}}; };
 #define B200_NV_KEYS_16 2
 template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {3, 256, 12, 2, 0}}; };
 #define B200_NV_RECORDS_8 2

@@ -62,6 +62,15 @@ __device__ __forceinline__ u128 ld_elem<u128>(const u128* p) {
     return r;
 }
 
+// store into global memory through the global state space (STG), not the generic one (ST):
+// the address of a run comes out of integer arithmetic, which nvcc otherwise stores through
+// the generic window check.  Peer-mapped receive buffers (K7) are global addresses too.
+__device__ __forceinline__ void st_global(unsigned long long addr, unsigned char v) { asm volatile("st.global.u8 [%0], %1;" ::"l"(addr), "r"((unsigned)v) : "memory"); }
+__device__ __forceinline__ void st_global(unsigned long long addr, unsigned short v) { asm volatile("st.global.u16 [%0], %1;" ::"l"(addr), "h"(v) : "memory"); }
+__device__ __forceinline__ void st_global(unsigned long long addr, unsigned int v) { asm volatile("st.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory"); }
+__device__ __forceinline__ void st_global(unsigned long long addr, unsigned long long v) { asm volatile("st.global.u64 [%0], %1;" ::"l"(addr), "l"(v) : "memory"); }
+__device__ __forceinline__ void st_global(unsigned long long addr, u128 v) { asm volatile("st.global.v2.u64 [%0], {%1, %2};" ::"l"(addr), "l"(v.lo), "l"(v.hi) : "memory"); }
+
 // ---------------------------------------------------------------------------
 // K1: all-digit histogram.  16-byte coalesced loads (LDG.128), four in flight
 // per thread; one privatised shared-memory histogram set per CTA, bumped with
@@ -276,10 +285,18 @@ struct PassArgs {
     uint32_t* ticket;                    // tile-id dispenser, zeroed
     uint32_t* stats;                     // [0] tiles that took the re-rank fallback
     uint32_t force_rerank;               // test hook: every tile takes the re-rank fallback (b200sort_debug_force_rerank)
+    uint32_t opaque_zero;                // always 0, but ptxas cannot know: see pass_s in rank_and_scatter
+    uint32_t stagger_ns;                 // experiment (B200SORT_STAGGER_NS): the second CTA to arrive on an SM in the first
+    uint32_t first_wave;                 //   wave (tickets < first_wave) waits this long, so that the two CTAs of an SM run out of phase
     typename Tr::Params prm;
 };
 
 constexpr int LB_BATCH = 8;
+
+// Bits of the ABL template parameter of the K3 kernels (VariantDesc::lbb >> 8).  Bits 0..4 are timing
+// ablations (results wrong on purpose); the bits from 5 up switch code paths that give the same result.
+constexpr int FEAT_STG = 32;     // write-out through st.global (STG) instead of generic stores (ST)
+constexpr int FEAT_NODOM = 64;   // scatter: plain atomics unless the tile or the warp has a dominant digit
 
 template <typename Tr, int THREADS, int ITEMS>
 struct PassSmem {
@@ -440,11 +457,18 @@ __device__ __forceinline__ u128 shfl_elem(u128 v, int src) {
 //     one more 1-wavefront load -- a shuffle is dearer than that (u32 0.756 vs 0.770).
 // (32-bit element offsets instead of the 64-bit addresses in sh.gptr were tried:
 // one wavefront less per warp instruction, but no gain -- v19.)
-template <typename Tr, int THREADS, int ITEMS, bool FULL, bool VERIFY>
+template <typename E>
+__device__ __forceinline__ void st_elem(unsigned long long addr, E v, bool stg) {
+    if (stg) st_global(addr, v);
+    else *reinterpret_cast<E*>(addr) = v;
+}
+
+template <typename Tr, int THREADS, int ITEMS, bool FULL, bool VERIFY, int FEAT = 0>
 __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& sh, const PassArgs<Tr>& a,
                                           uint32_t xf_out, uint32_t tile_n, int tid) {
     using E = typename Tr::elem_t;
     bool bad = false;
+    constexpr bool STG = (FEAT & FEAT_STG) != 0;
     const uint32_t n_valid = FULL ? (uint32_t)(THREADS * ITEMS) : tile_n;
     if constexpr (Tr::FEW_BUCKETS) {
         // long runs, expensive digit: copy run by run, no digit per key
@@ -454,7 +478,7 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
             const uint32_t lo = sh.excl[b], hi = lo + sh.cnt[b];
             const unsigned long long base = sh.gptr[b];
             for (uint32_t idx = lo + tid; idx < hi; idx += THREADS)
-                *reinterpret_cast<E*>(base + (unsigned long long)idx * sizeof(E)) = sh.tile[idx];
+                st_elem<E>(base + (unsigned long long)idx * sizeof(E), sh.tile[idx], STG);
         }
     } else if constexpr (sizeof(E) >= 8) {
         const int lane = tid & 31;
@@ -484,7 +508,7 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
             if (FULL || idx < n_valid) {
                 const unsigned d = Tr::digit(key, a.pass, a.prm);
                 if (xf_out) key = Tr::xform_out(key, a.prm);
-                *reinterpret_cast<E*>(sh.gptr[d] + (unsigned long long)idx * sizeof(E)) = key;
+                st_elem<E>(sh.gptr[d] + (unsigned long long)idx * sizeof(E), key, STG);
             }
             cur = below;
         }
@@ -501,7 +525,7 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
                 }
                 const unsigned d = Tr::digit(key, a.pass, a.prm);
                 if (xf_out) key = Tr::xform_out(key, a.prm);
-                *reinterpret_cast<E*>(sh.gptr[d] + (unsigned long long)idx * sizeof(E)) = key;
+                st_elem<E>(sh.gptr[d] + (unsigned long long)idx * sizeof(E), key, STG);
             }
         }
     }
@@ -670,6 +694,11 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     // a running count in a register the rest -- lane-ordered by construction.  The
     // other keys are few and take the atomic.  The partition kernel (2..16 buckets,
     // registers to spare) groups lanes with match_any when a tile has <= 3 buckets.
+    // launder() stops nvcc from keeping every key's counter address alive from the count phase,
+    // but ptxas still sees the same registers and value-numbers digit(e[i], pass) of both phases
+    // alike (spills at the 64-register cap).  The scatter extracts its digits with a shift amount
+    // ptxas cannot prove equal: pass ^ 0, the zero coming in as a kernel parameter.
+    const int pass_s = pass ^ (int)a.opaque_zero;
     if constexpr (Tr::FEW_BUCKETS) {
         uint32_t distinct = 0;
         if constexpr (FULL) {
@@ -705,22 +734,56 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
         // no digit above half of the tile: the digit of the warp's first key stands in
         // (any choice is correct; on sorted input, whose tiles straddle two runs, it
         // is the warp's own dominant digit)
-        const unsigned dom = (domw >> 8) == ((((tile + 1u) << 4) | (uint32_t)(pass & 15)) & 0xFFFFFFu) ? (domw & 0xFFu)
-                                                                      : __shfl_sync(FULL_MASK, Tr::digit(e[0], pass, a.prm), 0);
-        uint32_t dom_slot = my_hist[hidx(dom)];  // next free slot of that digit in this warp's range
-        const unsigned lane_lt = (1u << lane) - 1u;
+        const bool tile_dom = (domw >> 8) == ((((tile + 1u) << 4) | (uint32_t)(pass & 15)) & 0xFFFFFFu);
+        const unsigned d0 = Tr::digit(e[0], pass_s, a.prm);
+        const unsigned dom = tile_dom ? (domw & 0xFFu) : __shfl_sync(FULL_MASK, d0, 0);
+        // FEAT_NODOM: the ballot path costs every key ~10 instructions and a divergent
+        // branch around its atomic (the loop cannot be software-pipelined), which keys
+        // without a dominant digit pay for nothing.  Warp-uniform choice: ballot path
+        // if the tile has a dominant digit or a quarter of the warp's first row agrees
+        // with its first key (sorted / clustered input); plain atomics otherwise.
+        bool use_dom = true;
+        if constexpr ((ABL & FEAT_NODOM) != 0) use_dom = tile_dom || __popc(__ballot_sync(FULL_MASK, d0 == dom)) >= 8;
+        if (use_dom) {
+            uint32_t dom_slot = my_hist[hidx(dom)];  // next free slot of that digit in this warp's range
+            const unsigned lane_lt = (1u << lane) - 1u;
 #pragma unroll
-        for (int i = 0; i < ITEMS; ++i) {
-            const bool valid = FULL || wbase + i * 32 < tile_n;
-            const unsigned d = Tr::digit(e[i], pass, a.prm);
-            const bool is_dom = valid && d == dom;
-            const unsigned m = __ballot_sync(FULL_MASK, is_dom);
-            uint32_t slot = dom_slot + (uint32_t)__popc(m & lane_lt);
-            dom_slot += (uint32_t)__popc(m);
-            if (valid && !is_dom) slot = atomicAdd(&my_hist[hidx(d)], 1u);
-            if (valid) {
-                sh.tile[slot] = e[i];
-                if constexpr (Tr::NEEDS_STABLE) sh.ent[slot] = (d << 16) | (wbase + (uint32_t)i * 32u);
+            for (int i = 0; i < ITEMS; ++i) {
+                const bool valid = FULL || wbase + i * 32 < tile_n;
+                const unsigned d = Tr::digit(e[i], pass_s, a.prm);
+                const bool is_dom = valid && d == dom;
+                const unsigned m = __ballot_sync(FULL_MASK, is_dom);
+                uint32_t slot = dom_slot + (uint32_t)__popc(m & lane_lt);
+                dom_slot += (uint32_t)__popc(m);
+                if (valid && !is_dom) slot = atomicAdd(&my_hist[hidx(d)], 1u);
+                if (valid) {
+                    sh.tile[slot] = e[i];
+                    if constexpr (Tr::NEEDS_STABLE) sh.ent[slot] = (d << 16) | (wbase + (uint32_t)i * 32u);
+                }
+            }
+        } else {
+            // groups of SG keys: SG atomics in flight, then SG stores (the whole tile at once
+            // would need ITEMS slot registers on top of the keys: spills at the 64-register cap)
+            constexpr int SG = sizeof(E) >= 8 ? 4 : 6;
+#pragma unroll
+            for (int g = 0; g < ITEMS; g += SG) {
+                uint32_t slot[SG];
+#pragma unroll
+                for (int j = 0; j < SG; ++j) {
+                    const int i = g + j;
+                    if (i < ITEMS && (FULL || wbase + i * 32 < tile_n))
+                        slot[j] = atomicAdd(&my_hist[hidx(Tr::digit(e[i], pass_s, a.prm))], 1u);
+                }
+#pragma unroll
+                for (int j = 0; j < SG; ++j) {
+                    const int i = g + j;
+                    if (i < ITEMS && (FULL || wbase + i * 32 < tile_n)) {
+                        sh.tile[slot[j]] = e[i];
+                        if constexpr (Tr::NEEDS_STABLE)
+                            sh.ent[slot[j]] = (Tr::digit(e[i], pass_s, a.prm) << 16) | (wbase + (uint32_t)i * 32u);
+                    }
+                }
+                asm volatile("" ::: "memory");
             }
         }
     }
@@ -732,10 +795,10 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     // ---- coalesced run write-out; key-only passes check the order of the tile
     if (ABL & 4) return false;
     if ((!Tr::NEEDS_STABLE && pass == 0) || (ABL & 2)) {
-        write_out<Tr, WORKERS, ITEMS, FULL, false>(sh, a, pp.xf_out, tile_n, tid);
+        write_out<Tr, WORKERS, ITEMS, FULL, false, ABL>(sh, a, pp.xf_out, tile_n, tid);
         return false;
     }
-    return write_out<Tr, WORKERS, ITEMS, FULL, true>(sh, a, pp.xf_out, tile_n, tid);
+    return write_out<Tr, WORKERS, ITEMS, FULL, true, ABL>(sh, a, pp.xf_out, tile_n, tid);
 }
 
 template <typename Tr, int THREADS, int ITEMS, int MIN_BLOCKS, int LBB = LB_BATCH, int ABL = 0>
@@ -752,6 +815,19 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     if (threadIdx.x == 0) ticket = atomicAdd(a.ticket, 1u);
     const PassPlan pp = a.plan->pass[a.pass];
     if (pp.skip) return;
+    if (a.stagger_ns && threadIdx.x == 0 && ticket < a.first_wave && a.pass < 12) {
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        const unsigned bit = 1u << (smid & 31);
+        if (atomicOr(a.stats + 1 + a.pass * 5 + (smid >> 5), bit) & bit) {
+            unsigned long long t0, t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            do {
+                __nanosleep(200);
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            } while (t1 - t0 < a.stagger_ns);
+        }
+    }
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     PassShared<Tr, THREADS, ITEMS> sh(smem_raw, SM::TILE_BYTES);
