@@ -125,6 +125,12 @@ void b200sort_debug_force_rerank(int on);
  * passes in shared memory) instead of the K1-K2-K3 sequence; 0 turns that off so
  * that tests can drive the big path at small sizes too (1 restores). */
 void b200sort_debug_small_sort(int on);
+/* Key-only sorts of 1- and 2-byte keys (u8, i8, u16, i16; counting_sort, mod.rs:40-59) need no
+ * ranking: equal keys are bit-identical, so the library takes one value histogram and writes
+ * every value count[v] times (csrc/narrow_kernels.cuh).  0 sends these widths through the
+ * onesweep passes instead (as B200SORT_FLAG_NO_SKIP and the timed entry point always do), so that
+ * tests reach both; 1 restores. */
+void b200sort_debug_narrow_fill(int on);
 int b200sort_debug_reranked_tiles(void *d_tmp, size_t tmp_bytes, size_t n, int kind, size_t rec_bytes, void *stream,
                                   unsigned *out);
 

@@ -59,6 +59,10 @@ def lib() -> ctypes.CDLL:
         L.oracle_get_digit.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_uint]
         L.oracle_get_digit.restype = ctypes.c_int
         L.oracle_available_parallelism.restype = ctypes.c_int
+        L.oracle_sort0_records.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_int]
+        L.oracle_sort0_records.restype = ctypes.c_int
+        L.oracle_generate_uniform.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint64, ctypes.c_uint64]
+        L.oracle_generate_uniform.restype = ctypes.c_int
         _lib = L
     return _lib
 
@@ -95,6 +99,32 @@ def sort4_mt(buf: np.ndarray, kind: str, threads: int | None = None) -> None:
     rc = lib().oracle_sort4_mt(buf.ctypes.data, n, KINDS[kind], threads or available_parallelism())
     if rc:
         raise RuntimeError(f"oracle_sort4_mt rc={rc}")
+
+
+def sort0_records(buf: np.ndarray, rec_bytes: int, key_off: int, kind: str) -> None:
+    """In-place sequential LSD sort of (T, U) records of any shape: whole records of
+    rec_bytes bytes move, the key of kind `kind` sits at byte key_off
+    (radix_digits.rs:126-136 over mod.rs:182-212).  Stable."""
+    if not (buf.flags["C_CONTIGUOUS"] and buf.flags["WRITEABLE"]):
+        raise ValueError("oracle needs a writable C-contiguous buffer")
+    nbytes = buf.size * buf.itemsize
+    if nbytes % rec_bytes:
+        raise ValueError("buffer size is not a multiple of the record size")
+    rc = lib().oracle_sort0_records(buf.ctypes.data, nbytes // rec_bytes, rec_bytes, key_off, KINDS[kind])
+    if rc:
+        raise RuntimeError(f"oracle_sort0_records rc={rc}")
+
+
+def generate_uniform(n: int, kind: str, seed: int, index_base: int = 0) -> np.ndarray:
+    """The UNIFORM input family, generated on the host cores: the same
+    stream as radix_sort_b200.distr.uniform_host and the device generator."""
+    kb = KEY_BYTES[kind]
+    dt = {1: np.uint8, 2: np.uint16, 4: np.uint32, 8: np.uint64, 16: np.uint64}[kb]
+    out = np.empty((n, 2) if kb == 16 else (n,), dtype=dt)
+    rc = lib().oracle_generate_uniform(out.ctypes.data, n, kb, seed & (2**64 - 1), index_base)
+    if rc:
+        raise RuntimeError(f"oracle_generate_uniform rc={rc}")
+    return out
 
 
 def get_digit(elem_bytes: bytes, kind: str, index: int) -> int:

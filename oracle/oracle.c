@@ -25,6 +25,8 @@
  *   radix_sort  (production, native threads + 96-element write buffers)
  *                                 src/radix_sort/mod.rs:61-176    -> oracle_sort_mt
  *   radix_sort4 (rayon variant)   src/radix_sort/mod.rs:405-466   -> oracle_sort4_mt
+ *   (T,U) of any shape, sequential src/radix_sort/radix_digits.rs:126-136 + mod.rs:182-212
+ *                                                                 -> oracle_sort0_records
  *
  * Elements are moved bit-for-bit; the key transform lives only inside
  * get_digit, exactly as in the reference (radix_digits.rs:59,110-112).
@@ -313,6 +315,80 @@ int oracle_get_digit(const void *e, int kind, unsigned index) {
     case K_F64:  return (int)dg_f64((const uint64_t *)e, index);
     default: return -2;
     }
+}
+
+/* ---- general (T, U) records: key = field .0 at byte offset key_off ------------------
+ * radix_digits.rs:126-136 implements RadixDigits for ANY (T, U) with T: RadixDigits: the
+ * digit is the key field's, the whole tuple is moved (mod.rs:133,145,158).  Sequential LSD,
+ * the statement of mod.rs:182-212 with memcpy'd elements of rec_bytes bytes; `kind` names
+ * the key type.  Returns 0, -2 for an unknown kind, -3 for a key that does not fit. */
+static size_t kind_bytes(int kind) {
+    switch (kind) {
+    case K_U8: case K_I8: return 1;
+    case K_U16: case K_I16: return 2;
+    case K_U32: case K_I32: case K_F32: return 4;
+    case K_U64: case K_I64: case K_F64: return 8;
+    case K_U128: case K_I128: return 16;
+    default: return 0;
+    }
+}
+
+int oracle_sort0_records(void *data, size_t n, size_t rec_bytes, size_t key_off, int kind) {
+    const size_t kb = kind_bytes(kind);
+    if (kb == 0) return -2;
+    if (key_off + kb > rec_bytes) return -3;
+    if (n == 0) return 0;
+    unsigned char *a = (unsigned char *)data;
+    unsigned char *t = (unsigned char *)malloc(n * rec_bytes);
+    if (!t) return -1;
+    unsigned char *src = a, *dst = t;
+    for (unsigned d = 0; d < (unsigned)kb; ++d) {           /* NUMBER_OF_DIGITS = size_of::<T>() */
+        size_t hist[256] = {0};
+        for (size_t i = 0; i < n; ++i) {                     /* mod.rs:191-194 */
+            unsigned char key[16];
+            memcpy(key, src + i * rec_bytes + key_off, kb);  /* the tuple may sit at any alignment */
+            hist[oracle_get_digit(key, kind, d)]++;
+        }
+        size_t run = 0;                                      /* mod.rs:195-202 */
+        for (int g = 0; g < 256; ++g) { size_t c = hist[g]; hist[g] = run; run += c; }
+        for (size_t i = 0; i < n; ++i) {                     /* mod.rs:203-207 */
+            unsigned char key[16];
+            memcpy(key, src + i * rec_bytes + key_off, kb);
+            memcpy(dst + hist[oracle_get_digit(key, kind, d)]++ * rec_bytes, src + i * rec_bytes, rec_bytes);
+        }
+        unsigned char *x = src; src = dst; dst = x;          /* mod.rs:186-190 */
+    }
+    if (src != a) memcpy(a, src, n * rec_bytes);             /* odd digit count, mod.rs:209-211 */
+    free(t);
+    return 0;
+}
+
+/* ---- input generator (bench.py's CPU arms) ----------------------------------------
+ * The UNIFORM family of SURVEY.md 8(d): key i = low bytes of mix64(seed ^ mix64(i)),
+ * mix64 = the splitmix64 finaliser; the same stream as radix_sort_b200.distr.uniform_host
+ * and the device generator (inputs only: the reference draws from an unseeded thread_rng,
+ * main.rs:27).  key_bytes in {1, 2, 4, 8}; 16: lo = u, hi = mix64(u). */
+static inline uint64_t mix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+int oracle_generate_uniform(void *out, size_t n, int key_bytes, uint64_t seed, uint64_t index_base) {
+    if (key_bytes != 1 && key_bytes != 2 && key_bytes != 4 && key_bytes != 8 && key_bytes != 16) return -2;
+#pragma omp parallel for schedule(static)
+    for (size_t i = 0; i < n; ++i) {
+        const uint64_t u = mix64(seed ^ mix64(index_base + i));
+        switch (key_bytes) {
+        case 1: ((uint8_t *)out)[i] = (uint8_t)u; break;
+        case 2: ((uint16_t *)out)[i] = (uint16_t)u; break;
+        case 4: ((uint32_t *)out)[i] = (uint32_t)u; break;
+        case 8: ((uint64_t *)out)[i] = u; break;
+        default: ((uint64_t *)out)[2 * i] = u; ((uint64_t *)out)[2 * i + 1] = mix64(u); break;
+        }
+    }
+    return 0;
 }
 
 /* available_parallelism() stand-in (mod.rs:66-70). */

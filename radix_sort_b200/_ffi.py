@@ -41,6 +41,7 @@ PROTOTYPES = {
                                                    c_void_p, c_void_p, c_void_p]),
     "b200sort_debug_force_rerank": (None, [c_int]),
     "b200sort_debug_small_sort": (None, [c_int]),
+    "b200sort_debug_narrow_fill": (None, [c_int]),
     "b200sort_debug_reranked_tiles": (c_int, [c_void_p, c_size_t, c_size_t, c_int, c_size_t, c_void_p, POINTER(c_uint)]),
     "b200sort_partition_exchange_part_device": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_int, c_void_p, c_int,
                                                         c_void_p, c_void_p, ctypes.c_uint, c_int, c_void_p]),

@@ -218,6 +218,12 @@ def debug_small_sort(on: bool) -> None:
     _ffi.lib().b200sort_debug_small_sort(1 if on else 0)
 
 
+def debug_narrow_fill(on: bool) -> None:
+    """Test hook: False sends key-only 1- and 2-byte keys through the onesweep passes instead of
+    the histogram + fill path (csrc/narrow_kernels.cuh)."""
+    _ffi.lib().b200sort_debug_narrow_fill(1 if on else 0)
+
+
 def debug_reranked_tiles(workspace, n: int, kind, rec_bytes: int = 0) -> int:
     """Tiles of the last sort run on `workspace` (a CUDA tensor) that took the slow path."""
     import torch

@@ -42,6 +42,8 @@ std::atomic<int> g_force_rerank{0};
 bool force_rerank() { return g_force_rerank.load(std::memory_order_relaxed) != 0; }
 std::atomic<int> g_small_sort{1};
 bool small_sort_enabled() { return g_small_sort.load(std::memory_order_relaxed) != 0; }
+std::atomic<int> g_narrow_fill{1};
+bool narrow_fill_enabled() { return g_narrow_fill.load(std::memory_order_relaxed) != 0; }
 int variant_override(int family, int elem_bytes) {
     return g_variant[family][elem_bytes].load(std::memory_order_relaxed) - 1;
 }
@@ -584,6 +586,8 @@ int b200sort_partition_exchange_part_device(const void* d_in, void* d_tmp, size_
 unsigned long long b200sort_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 void b200sort_debug_small_sort(int on) { g_small_sort.store(on ? 1 : 0, std::memory_order_relaxed); }
+
+void b200sort_debug_narrow_fill(int on) { g_narrow_fill.store(on ? 1 : 0, std::memory_order_relaxed); }
 
 void b200sort_debug_force_rerank(int on) { g_force_rerank.store(on ? 1 : 0, std::memory_order_relaxed); }
 

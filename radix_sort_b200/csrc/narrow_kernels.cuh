@@ -1,0 +1,215 @@
+// narrow_kernels.cuh -- key-only sorts of 1- and 2-byte keys without any ranking.
+//
+// Equal keys are bit-identical (radix_digits.rs:7-21,55-69: the ordered image is a
+// bijection of the bit pattern), so the sorted slice is a function of the value
+// histogram alone: value v, count[v] times, in get_digit's order.  That is the
+// reference's own counting_sort (mod.rs:40-59: histogram, prefix, fill) taken to 16
+// bits: one read of the keys (K1n) + one streaming write (K3n) = 2 s bytes per key
+// instead of s (1 + 2 D) through the onesweep passes, and no shared-memory ranking.
+//
+//   K1n  hist_values_kernel   full histogram over all 2^(8s) values of the ordered key
+//          u8 : 256 bins, every bin replicated 32 times (lane-private banks), like K1
+//          u16: 65536 u32 bins are 256 KB -- more than one SM has.  Two CTAs share a
+//               slab of the input, each counts the values whose top bit is its own
+//               (32768 bins = 128 KB of shared memory each); the slab is read twice,
+//               the second time mostly from L2.
+//   K2n  scan_values_kernel   exclusive prefix over the bins -> offs[NV + 1]
+//   K3n  fill_values_kernel   CTA b owns output elements [b C, (b + 1) C): finds its first
+//          value by a two-level search of offs, then walks the values: short runs are
+//          written by one thread each, long runs by the whole CTA with 16-byte stores.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "key_traits.cuh"
+
+namespace b200 {
+
+template <typename U> struct NarrowCfg;
+template <> struct NarrowCfg<uint8_t> {
+    static constexpr int NV = 256, THREADS = 1024, R = 32, SPLIT = 1;
+    static constexpr size_t SMEM = (size_t)NV * R * 4;
+};
+template <> struct NarrowCfg<uint16_t> {
+    static constexpr int NV = 65536, THREADS = 1024, R = 1, SPLIT = 2;
+    static constexpr size_t SMEM = (size_t)(NV / SPLIT) * 4;
+};
+
+// K1n.  grid = SPLIT * slabs; CTA (slab, half) counts the keys of its slab whose ordered
+// value falls into its half of the value range.  hist: NV u64 bins, zeroed.
+template <typename U>
+__global__ void __launch_bounds__(NarrowCfg<U>::THREADS)
+hist_values_kernel(const U* __restrict__ in, size_t n, unsigned long long* __restrict__ hist, int xf) {
+    using C = NarrowCfg<U>;
+    constexpr int VEC = 16 / (int)sizeof(U);
+    extern __shared__ __align__(16) uint32_t bins[];
+    const int tid = threadIdx.x;
+    constexpr int NB = C::NV / C::SPLIT * C::R;
+    for (int i = tid; i < NB; i += C::THREADS) bins[i] = 0;
+    __syncthreads();
+    const unsigned half = blockIdx.x % C::SPLIT;
+    const unsigned slab = blockIdx.x / C::SPLIT, slabs = gridDim.x / C::SPLIT;
+    auto count = [&](U raw) {
+        const unsigned v = to_ordered_rt<U>(raw, xf);
+        if constexpr (C::SPLIT == 1) {
+            atomicAdd(&bins[v * C::R + (tid & (C::R - 1))], 1u);
+        } else {
+            if ((v >> 15) == half) atomicAdd(&bins[v & 0x7FFFu], 1u);
+        }
+    };
+    auto count_vec = [&](uint4 q) {
+        union { uint4 q; U e[VEC]; } u;
+        u.q = q;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) count(u.e[j]);
+    };
+    const uintptr_t addr = (uintptr_t)in;
+    size_t head = ((16 - (addr & 15)) & 15) / sizeof(U);
+    if (head > n) head = n;
+    const uint4* vec = reinterpret_cast<const uint4*>(in + head);
+    const size_t nvec = (n - head) / VEC;
+    const size_t tail = head + nvec * VEC;
+    // slab = a contiguous run of vectors, so that the two CTAs of a slab walk the same lines
+    const size_t per = (nvec + slabs - 1) / slabs;
+    const size_t lo = (size_t)slab * per, hi = lo + per < nvec ? lo + per : nvec;
+    size_t i = lo + tid;
+    for (; i + 3 * (size_t)C::THREADS < hi; i += 4 * (size_t)C::THREADS) {
+        const uint4 a = __ldg(vec + i), b = __ldg(vec + i + C::THREADS), c = __ldg(vec + i + 2 * C::THREADS),
+                    d = __ldg(vec + i + 3 * C::THREADS);
+        count_vec(a); count_vec(b); count_vec(c); count_vec(d);
+    }
+    for (; i < hi; i += C::THREADS) count_vec(__ldg(vec + i));
+    if (slab == 0) {
+        for (size_t j = tid; j < head; j += C::THREADS) count(in[j]);
+        for (size_t j = tail + tid; j < n; j += C::THREADS) count(in[j]);
+    }
+    __syncthreads();
+    if constexpr (C::SPLIT == 1) {
+        for (int k = tid; k < C::NV; k += C::THREADS) {
+            uint32_t c = 0;
+#pragma unroll
+            for (int r = 0; r < C::R; ++r) c += bins[k * C::R + ((r + tid) & (C::R - 1))];
+            if (c) atomicAdd(&hist[k], (unsigned long long)c);
+        }
+    } else {
+        for (int k = tid; k < C::NV / C::SPLIT; k += C::THREADS) {
+            const uint32_t c = bins[k];
+            if (c) atomicAdd(&hist[half * (C::NV / C::SPLIT) + k], (unsigned long long)c);
+        }
+    }
+}
+
+// K2n: one CTA of 1024 threads; offs[v] = keys with an ordered value below v, offs[NV] = n.
+template <int NV>
+__global__ void __launch_bounds__(1024)
+scan_values_kernel(const unsigned long long* __restrict__ hist, unsigned long long* __restrict__ offs) {
+    constexpr int PER = NV >= 1024 ? NV / 1024 : 1;
+    __shared__ unsigned long long warp_tot[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long local = 0;
+    if (tid * PER < NV)
+        for (int j = 0; j < PER; ++j) local += hist[tid * PER + j];
+    unsigned long long x = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+        if (lane >= o) x += y;
+    }
+    if (lane == 31) warp_tot[warp] = x;
+    __syncthreads();
+    unsigned long long base = 0;
+    for (int w = 0; w < warp; ++w) base += warp_tot[w];
+    unsigned long long run = base + x - local;
+    if (tid * PER < NV)
+        for (int j = 0; j < PER; ++j) {
+            offs[tid * PER + j] = run;
+            run += hist[tid * PER + j];
+        }
+    if (tid == 1023) offs[NV] = run;
+}
+
+// K3n.  out may be the buffer the keys were read from (the histogram has consumed them).
+template <typename U>
+__global__ void __launch_bounds__(1024)
+fill_values_kernel(U* __restrict__ out, size_t n, const unsigned long long* __restrict__ offs, int xf) {
+    using C = NarrowCfg<U>;
+    constexpr int NV = C::NV;
+    constexpr int THREADS = 1024;
+    constexpr int VEC = 16 / (int)sizeof(U);
+    constexpr int LONG_RUN = 256;   // elements from which a run is written by the whole CTA
+    constexpr int QCAP = 1024;
+    __shared__ unsigned s_first;
+    __shared__ unsigned s_qn;
+    __shared__ unsigned q_val[QCAP];
+    __shared__ unsigned long long q_lo[QCAP], q_hi[QCAP];
+    const int tid = threadIdx.x;
+    // chunk of the output, whole 16-byte vectors of the (possibly unaligned) buffer
+    const size_t chunk = ((n + gridDim.x - 1) / gridDim.x + 4095) / 4096 * 4096;
+    const size_t lo = (size_t)blockIdx.x * chunk;
+    if (lo >= n) return;
+    const size_t hi = lo + chunk < n ? lo + chunk : n;
+    // first value of the chunk: the largest v with offs[v] <= lo.  Level 1: 1024 probes NV / 1024 apart
+    // (the last one that passes is found with a ballot per warp + one shared word), level 2: the bracket.
+    if (tid == 0) s_first = 0;
+    __syncthreads();
+    constexpr int STRIDE = NV >= THREADS ? NV / THREADS : 1;
+    if (tid * STRIDE < NV && offs[tid * STRIDE] <= lo) atomicMax(&s_first, (unsigned)(tid * STRIDE));
+    __syncthreads();
+    if (STRIDE > 1) {
+        const unsigned b0 = s_first;
+        __syncthreads();
+        if (tid < STRIDE && offs[b0 + tid] <= lo) atomicMax(&s_first, b0 + (unsigned)tid);
+        __syncthreads();
+    }
+    unsigned vcur = s_first;
+    for (;;) {
+        if (tid == 0) s_qn = 0;
+        __syncthreads();
+        const unsigned v = vcur + (unsigned)tid;
+        unsigned long long s = 0, e = 0;
+        if (v < (unsigned)NV) {
+            s = offs[v];
+            e = offs[v + 1];
+            if (s < lo) s = lo;
+            if (e > hi) e = hi;
+        }
+        const bool any = v < (unsigned)NV && e > s;
+        if (any) {
+            const U val = from_ordered_rt<U>((U)v, xf);
+            if (e - s < (unsigned long long)LONG_RUN) {
+                for (unsigned long long p = s; p < e; ++p) out[p] = val;
+            } else {
+                const unsigned slot = atomicAdd(&s_qn, 1u);
+                q_val[slot] = val;
+                q_lo[slot] = s;
+                q_hi[slot] = e;
+            }
+        }
+        // done when the last value of this batch already ends at or past the chunk's end
+        const unsigned vlast = vcur + THREADS - 1 < (unsigned)NV - 1 ? vcur + THREADS - 1 : (unsigned)NV - 1;
+        const bool done = offs[vlast + 1] >= hi || vcur + THREADS >= (unsigned)NV;
+        __syncthreads();
+        const unsigned qn = s_qn;
+        for (unsigned k = 0; k < qn; ++k) {
+            const U val = (U)q_val[k];
+            const unsigned long long s2 = q_lo[k], e2 = q_hi[k];
+            // head up to 16-byte alignment, vectors, tail
+            const uintptr_t a0 = (uintptr_t)(out + s2);
+            unsigned long long hd = ((16 - (a0 & 15)) & 15) / sizeof(U);
+            if (hd > e2 - s2) hd = e2 - s2;
+            const unsigned long long nv = (e2 - s2 - hd) / VEC;
+            const unsigned long long tl = s2 + hd + nv * VEC;
+            if ((unsigned long long)tid < hd) out[s2 + tid] = val;
+            uint32_t w = sizeof(U) == 1 ? 0x01010101u * (uint32_t)val : 0x00010001u * (uint32_t)val;
+            const uint4 vv = make_uint4(w, w, w, w);
+            uint4* vp = reinterpret_cast<uint4*>(out + s2 + hd);
+            for (unsigned long long i = tid; i < nv; i += THREADS) vp[i] = vv;
+            if (tl + tid < e2) out[tl + tid] = val;
+        }
+        if (done) return;
+        vcur += THREADS;
+        __syncthreads();
+    }
+}
+
+}  // namespace b200

@@ -16,6 +16,7 @@
 #include <vector>
 
 #include "../../include/b200sort.h"
+#include "narrow_kernels.cuh"
 #include "sort_kernels.cuh"
 #include "stream_kernel.cuh"
 
@@ -28,6 +29,7 @@ void count_launch();
 int variant_override(int family, int elem_bytes);  // -1 = library default
 bool force_rerank();                               // test hook (b200sort_debug_force_rerank)
 bool small_sort_enabled();                         // test hook (b200sort_debug_small_sort)
+bool narrow_fill_enabled();                        // test hook (b200sort_debug_narrow_fill)
 
 #define B200_CU(call)                                               \
     do {                                                            \
@@ -59,32 +61,35 @@ struct VariantDesc { int kernel, threads, items, min_blocks, lbb; };  // lbb = p
 
 template <int FAM, int W> struct Variants;
 #define B200_NV_KEYS_1 2
-template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}, {3, 512, 32, 2, 0}}; };
+template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0x2000}, {3, 512, 32, 2, 0}}; };
 #define B200_NV_KEYS_2 2
-template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}, {3, 512, 24, 2, 0}}; };
-// (lbb bits 8+: FEAT_STG = 32 -> 0x2000, FEAT_NODOM = 64 -> 0x4000)
-#define B200_NV_KEYS_4 9
-template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 26, 2, 0}, {3, 512, 22, 2, 0}, {0, 512, 22, 2, 0}, {0, 512, 16, 2, 0},
-    {0, 512, 26, 2, 0x2000}, {0, 512, 26, 2, 0x4000}, {0, 512, 26, 2, 0x6000}, {0, 1024, 26, 1, 0x6000}, {0, 1024, 20, 1, 0x6000}}; };
-#define B200_NV_KEYS_8 8
-template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {3, 512, 16, 2, 0}, {0, 256, 20, 3, 0},
-    {0, 512, 16, 2, 0x2000}, {0, 512, 16, 2, 0x4000}, {0, 512, 16, 2, 0x6000}, {0, 1024, 16, 1, 0x6000}, {0, 1024, 12, 1, 0x6000}}; };
+template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0x2000}, {3, 512, 24, 2, 0}}; };
+// (lbb bits 8+ = the ABL / FEAT mask of sort_kernels.cuh: FEAT_STG = 32 -> 0x2000, FEAT_NODOM = 64 -> 0x4000)
+// Round-2 sweeps (profiles/r02_sweep_v30_v32.README.txt): st.global write-out +2.9 % on u32, neutral on u64 -> default;
+// plain-atomic scatter (FEAT_NODOM), 1024-thread tiles with one CTA per SM (-9 %), 32- and 40-register shapes with
+// 64 / 48 resident warps (-19 % / -1..8 %) all lose and are not shipped (1024x26x1, 1024x16x1, 1024x8x2, 768x10x2 ...).
+#define B200_NV_KEYS_4 6
+template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 26, 2, 0x2000}, {3, 512, 22, 2, 0}, {0, 512, 22, 2, 0}, {0, 512, 16, 2, 0},
+    {0, 512, 26, 2, 0x6000}, {0, 512, 26, 2, 0}}; };
+#define B200_NV_KEYS_8 5
+template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0x2000}, {3, 512, 16, 2, 0}, {0, 256, 20, 3, 0},
+    {0, 512, 16, 2, 0x6000}, {0, 512, 16, 2, 0}}; };
 #define B200_NV_KEYS_16 2
-template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {3, 256, 12, 2, 0}}; };
+template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0x2000}, {3, 256, 12, 2, 0}}; };
 #define B200_NV_RECORDS_8 2
-template <> struct Variants<FAM_RECORDS, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0}, {3, 512, 12, 2, 0}}; };
+template <> struct Variants<FAM_RECORDS, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0x2000}, {3, 512, 12, 2, 0}}; };
 #define B200_NV_RECORDS_16 2
-template <> struct Variants<FAM_RECORDS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}, {3, 256, 12, 2, 0}}; };
+template <> struct Variants<FAM_RECORDS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0x2000}, {3, 256, 12, 2, 0}}; };
 #define B200_NV_PARTITION_1 1
-template <> struct Variants<FAM_PARTITION, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}}; };
+template <> struct Variants<FAM_PARTITION, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0x2000}}; };
 #define B200_NV_PARTITION_2 1
-template <> struct Variants<FAM_PARTITION, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}}; };
+template <> struct Variants<FAM_PARTITION, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0x2000}}; };
 #define B200_NV_PARTITION_4 1
-template <> struct Variants<FAM_PARTITION, 4> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}}; };
+template <> struct Variants<FAM_PARTITION, 4> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0x2000}}; };
 #define B200_NV_PARTITION_8 1
-template <> struct Variants<FAM_PARTITION, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0}}; };
+template <> struct Variants<FAM_PARTITION, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0x2000}}; };
 #define B200_NV_PARTITION_16 1
-template <> struct Variants<FAM_PARTITION, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}}; };
+template <> struct Variants<FAM_PARTITION, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0x2000}}; };
 
 template <int FAM, int W> constexpr int num_variants() { return (int)(sizeof(Variants<FAM, W>::v) / sizeof(VariantDesc)); }
 
@@ -146,14 +151,16 @@ struct PassLauncher {
 // (the partition family always writes to a caller-named destination: no tmp region)
 //                                          ^--------- zeroed by one memset ---------------^
 struct Layout {
-    size_t tmp_off, bins_off, plan_off, hist_off, ticket_off, stats_off, lb_off, total;
+    size_t tmp_off, bins_off, plan_off, hist_off, ticket_off, stats_off, lb_off, narrow_off, total;
     size_t zero_off, zero_bytes;
     int portions;
     size_t portion_elems;  // elements per portion (multiple of tile)
     size_t tiles_total;    // tiles over all portions (one pass)
 };
 
-inline Layout make_layout(size_t n, size_t elem_bytes, int digits, int tile, bool with_tmp = true) {
+// narrow_bins: 256 / 65536 for key-only 1- / 2-byte keys (value histogram + prefix of the counting
+// path, narrow_kernels.cuh: NV u64 bins + NV + 1 u64 offsets, after everything else), else 0
+inline Layout make_layout(size_t n, size_t elem_bytes, int digits, int tile, bool with_tmp = true, size_t narrow_bins = 0) {
     Layout L{};
     const size_t max_portion = ((size_t)LB_VALUE_MASK / tile) * tile;  // < 2^30, whole tiles
     L.portion_elems = max_portion;
@@ -172,9 +179,10 @@ inline Layout make_layout(size_t n, size_t elem_bytes, int digits, int tile, boo
     L.ticket_off = off; off = align_up(off + (size_t)digits * L.portions * 4, 256);
     L.stats_off = off;  off += 256;
     L.lb_off = off;     off = align_up(off + (size_t)(with_tmp ? 2 : 1) * L.tiles_total * RADIX * 4, 256);  // two halves, swapped per executed pass
-    L.total = off;
     L.zero_off = L.hist_off;
-    L.zero_bytes = L.total - L.hist_off;
+    L.zero_bytes = off - L.hist_off;
+    L.narrow_off = off; off = align_up(off + (narrow_bins ? (2 * narrow_bins + 1) * 8 : 0), 256);
+    L.total = off;
     return L;
 }
 

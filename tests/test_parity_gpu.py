@@ -112,6 +112,62 @@ def test_small_sizes_through_the_big_path(kind, cuda):
         rs.debug_small_sort(True)
 
 
+# ---- 1- and 2-byte keys: value histogram + fill (csrc/narrow_kernels.cuh; counting_sort, mod.rs:40-59) ----
+
+NARROW = ["u8", "i8", "u16", "i16"]
+
+
+@pytest.mark.parametrize("kind", NARROW)
+def test_narrow_keys_counting_path(kind, cuda):
+    """The default route of key-only u8/i8/u16/i16 above the small-sort size: K1n + K2n + K3n.
+    Sizes around the fill kernel's chunking (4096-element granules, 65536 per CTA, 296 CTAs),
+    unaligned slices, and value distributions from one value to all of them."""
+    import torch
+    dt = {"u8": np.uint8, "i8": np.int8, "u16": np.uint16, "i16": np.int16}[kind]
+    launches0 = rs.launch_count()
+    for n in (4097, 65535, 65536, 65537, 1_000_003, (1 << 22) + 5, 296 * 65536 + 4097):
+        _check_device(_ref.random_keys(kind, n, seed=n), kind, cuda)
+    rng = np.random.default_rng(5)
+    n = 3_000_001
+    cases = {
+        "all_equal": np.full(n, -7 if kind[0] == "i" else 200, dtype=dt),
+        "two_values": rng.choice(np.array([1, np.iinfo(dt).max], dtype=dt), size=n),
+        "extremes": rng.choice(np.array([np.iinfo(dt).min, -1 if kind[0] == "i" else 1, 0, np.iinfo(dt).max], dtype=dt), size=n),
+        "ascending": np.arange(n).astype(dt),
+        "low_values": (rng.integers(0, 37, size=n)).astype(dt),
+    }
+    for name, a in cases.items():
+        _check_device(a, kind, cuda)
+        _check_host(a, kind)
+    # slices that start 1..3 elements into an allocation (head / tail handling of the 16-byte vectors)
+    base = _ref.random_keys(kind, 500_011, seed=9)
+    t_all = torch.from_numpy(base).to(cuda)
+    for off in (1, 2, 3, 7):
+        t = t_all[off:off + 400_000]
+        a = t.cpu().numpy().copy()
+        want = a.copy()
+        cpu_oracle.sort0(want, kind)
+        rs.radix_sort(t, _kind(kind))
+        torch.cuda.synchronize()
+        assert _ref.same_bits(t.cpu().numpy(), want), f"offset {off}"
+        # the elements around the slice are untouched
+        assert _ref.same_bits(t_all[:off].cpu().numpy(), base[:off])
+        base = t_all.cpu().numpy().copy()
+    assert rs.launch_count() > launches0
+
+
+@pytest.mark.parametrize("kind", NARROW)
+def test_narrow_keys_through_the_onesweep_passes(kind, cuda):
+    """The same widths with the counting path switched off: K1-K2-K3 as for every other width."""
+    rs.debug_narrow_fill(False)
+    try:
+        for n in (4097, 100_003, 1_000_003):
+            _check_device(_ref.random_keys(kind, n, seed=n + 1), kind, cuda)
+        _check_device(np.full(70_000, 3, dtype={"u8": np.uint8, "i8": np.int8, "u16": np.uint16, "i16": np.int16}[kind]), kind, cuda)
+    finally:
+        rs.debug_narrow_fill(True)
+
+
 @pytest.mark.parametrize("small", [True, False])
 @pytest.mark.parametrize("key_kind,dt", [("u32", np.uint32), ("i64", np.int64), ("f32", np.float32)])
 def test_small_record_slices_stay_stable(key_kind, dt, small, cuda):
