@@ -98,6 +98,13 @@ int b200sort_keys_host(void *keys, size_t n, int kind);
  * (tests use both). */
 int b200sort_set_host_pipeline_min_bytes(size_t bytes);
 
+/* The host entry points keep the device blocks they staged through (2 x data +
+ * workspace: ~17-25 GB after one 1 B-key u64 call) for the next call, and the
+ * communicator keeps its receive buffers.  This frees every block of the host-path
+ * pool that is not in use right now (all devices); the next call allocates again.
+ * Returns B200SORT_OK. */
+int b200sort_release_cached_memory(void);
+
 /* Key-value records, key = field 0 of a `(K, V)` tuple (radix_digits.rs:126-136;
  * call sites tests.rs:182, main.rs:112,123).  Stable.  rec_bytes is the whole
  * record (8 for (u32,u32), 16 for (u64,u64)); the key of `kind` sits at byte
@@ -179,10 +186,13 @@ int b200sort_fingerprint(const void *d_keys, size_t n, int kind, uint64_t *d_out
 int b200sort_count_unsorted(const void *d_keys, size_t n, int kind, uint64_t *d_out,
                             void *stream);
 
-/* ---- multi-GPU building blocks (one process per GPU; the exchange itself is
- * NCCL all-to-all driven from the host side, radix_sort_b200/mgpu.py) -------- */
+/* ---- multi-GPU building blocks (one process per GPU: radix_sort_b200/mgpu.py drives
+ * them; the exchange is K7 storing into the destinations' receive buffers over NVLink
+ * -- b200sort_partition_exchange_device below -- with K7 into a send buffer + the
+ * caller's NCCL all-to-all as the fallback when peer memory cannot be mapped) ---- */
 
-/* K7: stable partition of d_in[0..n) by destination rank.  A key goes to rank
+/* K7: partition of d_in[0..n) by destination rank (the order inside a destination is
+ * NOT specified: every destination is sorted next, and equal keys are bit-identical).  A key goes to rank
  * r = #{j : splitters[j] <= key}, 0 <= r <= nsplit (nsplit <= 15), compared in
  * get_digit's order,
  * where `splitters` are nsplit ascending keys of `kind` in HOST memory, given

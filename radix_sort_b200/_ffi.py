@@ -22,6 +22,7 @@ PROTOTYPES = {
     "b200sort_keys_device_ex": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_int, c_void_p, c_uint]),
     "b200sort_keys_host": (c_int, [c_void_p, c_size_t, c_int]),
     "b200sort_set_host_pipeline_min_bytes": (c_int, [c_size_t]),
+    "b200sort_release_cached_memory": (c_int, []),
     "b200sort_records_temp_bytes": (c_size_t, [c_size_t, c_size_t, c_int]),
     "b200sort_records_device": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_size_t, c_size_t, c_int, c_void_p]),
     "b200sort_records_host": (c_int, [c_void_p, c_size_t, c_size_t, c_size_t, c_int]),
@@ -73,11 +74,18 @@ def lib() -> ctypes.CDLL:
         if _build.needs_build():
             try:
                 path = _build.build()
-            except Exception as exc:  # stale .so + no nvcc is still usable; no .so is fatal
+            except Exception as exc:
                 if not os.path.exists(_build.LIB):
                     raise RuntimeError(
                         "libb200sort.so is missing and could not be built; the CUDA library is "
                         "the only implementation (no CPU fallback)") from exc
+                # a library older than the sources would run old kernels under new prototypes
+                if os.environ.get("B200SORT_ALLOW_STALE") != "1":
+                    raise RuntimeError(
+                        "the sources of libb200sort.so changed and the rebuild failed; refusing to load the stale "
+                        "library (set B200SORT_ALLOW_STALE=1 to load it anyway)") from exc
+                import warnings
+                warnings.warn("loading a STALE libb200sort.so (B200SORT_ALLOW_STALE=1): the sources changed and the rebuild failed")
         L = ctypes.CDLL(path)
         for name, (res, args) in PROTOTYPES.items():
             fn = getattr(L, name)  # AttributeError if the .so lacks a declared symbol

@@ -208,6 +208,11 @@ def set_host_pipeline_min_bytes(nbytes: int) -> None:
     check(_ffi.lib().b200sort_set_host_pipeline_min_bytes(int(nbytes)))
 
 
+def release_cached_memory() -> None:
+    """Free the device blocks the host entry points keep between calls (b200sort_release_cached_memory)."""
+    check(_ffi.lib().b200sort_release_cached_memory())
+
+
 def debug_force_rerank(on: bool) -> None:
     """Test hook: every K3 tile of every later sort takes the ballot re-rank slow path."""
     _ffi.lib().b200sort_debug_force_rerank(1 if on else 0)

@@ -489,6 +489,27 @@ int b200sort_keys_host(void* keys, size_t n, int kind) {
     });
 }
 
+int b200sort_release_cached_memory(void) {
+    std::vector<PoolBlock> idle;
+    {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        for (int i = (int)g_pool.size() - 1; i >= 0; --i)
+            if (!g_pool[i].busy) {
+                idle.push_back(g_pool[i]);
+                g_pool.erase(g_pool.begin() + i);
+            }
+    }
+    int prev = -1;
+    cudaGetDevice(&prev);
+    for (auto& b : idle) {
+        cudaSetDevice(b.dev);
+        cudaFree(b.p);
+    }
+    if (prev >= 0) cudaSetDevice(prev);
+    cudaGetLastError();
+    return B200SORT_OK;
+}
+
 int b200sort_set_host_pipeline_min_bytes(size_t bytes) {
     g_pipeline_min_bytes.store(bytes, std::memory_order_relaxed);
     return B200SORT_OK;

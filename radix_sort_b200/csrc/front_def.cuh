@@ -138,15 +138,24 @@ int sort_front(const SortCall& c) {
                 B200_CU(cudaFuncSetAttribute(hk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NC::SMEM));
                 configured.fetch_or(1u << (dev & 31), std::memory_order_release);
             }
-            B200_CU(cudaMemsetAsync(vhist, 0, (size_t)NC::NV * 8, st));
-            // u8: two CTAs per SM; u16: one CTA per SM, in pairs that share a slab of the input
-            unsigned slabs = (unsigned)(NC::SPLIT == 1 ? 2 * sms : sms / 2);
-            const size_t vecs = (n * W + 15) / 16;
-            const size_t want = (vecs + (size_t)NC::THREADS * 4 - 1) / ((size_t)NC::THREADS * 4);
-            if ((size_t)slabs > want) slabs = (unsigned)std::max<size_t>(1, want);
-            hk<<<slabs * NC::SPLIT, NC::THREADS, NC::SMEM, st>>>(d_elems, n, vhist, c.xf);
+            uint32_t* partial = reinterpret_cast<uint32_t*>(ws + L.narrow_partial_off);
+            unsigned slabs;
+            if constexpr (NC::SPLIT == 1) {  // u8: two CTAs per SM, one global atomic per bin and CTA
+                B200_CU(cudaMemsetAsync(vhist, 0, (size_t)NC::NV * 8, st));
+                const size_t vecs = (n * W + 15) / 16;
+                const size_t want = (vecs + (size_t)NC::THREADS * 4 - 1) / ((size_t)NC::THREADS * 4);
+                slabs = (unsigned)std::max<size_t>(1, std::min<size_t>(2 * (size_t)sms, want));
+            } else {                         // u16: one CTA per SM, in pairs that share a slab of the input
+                slabs = narrow_slabs16(n, sms);
+            }
+            hk<<<slabs * NC::SPLIT, NC::THREADS, NC::SMEM, st>>>(d_elems, n, vhist, partial, c.xf);
             count_launch();
             B200_CU(cudaGetLastError());
+            if constexpr (NC::SPLIT == 2) {
+                reduce_partials_kernel<<<NC::NV / 1024, 1024, 0, st>>>(partial, slabs, NC::NV, vhist);
+                count_launch();
+                B200_CU(cudaGetLastError());
+            }
             scan_values_kernel<NC::NV><<<1, 1024, 0, st>>>(vhist, voffs);
             count_launch();
             B200_CU(cudaGetLastError());

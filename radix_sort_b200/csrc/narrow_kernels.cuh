@@ -12,7 +12,8 @@
 //          u16: 65536 u32 bins are 256 KB -- more than one SM has.  Two CTAs share a
 //               slab of the input, each counts the values whose top bit is its own
 //               (32768 bins = 128 KB of shared memory each); the slab is read twice,
-//               the second time mostly from L2.
+//               the second time mostly from L2.  Per-slab counts are stored, then summed
+//               by reduce_partials_kernel.
 //   K2n  scan_values_kernel   exclusive prefix over the bins -> offs[NV + 1]
 //   K3n  fill_values_kernel   CTA b owns output elements [b C, (b + 1) C): finds its first
 //          value by a two-level search of offs, then walks the values: short runs are
@@ -35,11 +36,28 @@ template <> struct NarrowCfg<uint16_t> {
     static constexpr size_t SMEM = (size_t)(NV / SPLIT) * 4;
 };
 
+constexpr int NARROW_MAX_SLABS = 80;  // u16: slabs of the input (two CTAs each); B200: 148 SMs -> 74
+
+// slabs the u16 histogram is taken over for n keys on a device with `sms` SMs (host and layout agree on it)
+inline unsigned narrow_slabs16(size_t n, int sms) {
+    const size_t vecs = (n * 2 + 15) / 16;
+    size_t want = (vecs + 4095) / 4096;
+    if (want < 1) want = 1;
+    size_t cap = (size_t)(sms / 2 < 1 ? 1 : sms / 2);
+    if (cap > (size_t)NARROW_MAX_SLABS) cap = NARROW_MAX_SLABS;
+    return (unsigned)(want < cap ? want : cap);
+}
+
 // K1n.  grid = SPLIT * slabs; CTA (slab, half) counts the keys of its slab whose ordered
-// value falls into its half of the value range.  hist: NV u64 bins, zeroed.
+// value falls into its half of the value range.
+//   u8 : hist = NV u64 bins, zeroed, bumped with one global atomic per bin and CTA.
+//   u16: `partial` = [slab][NV] u32, every CTA stores its 32768 counts with plain coalesced stores
+//        (148 CTAs x 32768 u64 atomics on the same 65536 addresses took 0.2 ms -- more than the
+//        whole histogram of 2^27 keys); reduce_partials_kernel adds the slabs up.
 template <typename U>
 __global__ void __launch_bounds__(NarrowCfg<U>::THREADS)
-hist_values_kernel(const U* __restrict__ in, size_t n, unsigned long long* __restrict__ hist, int xf) {
+hist_values_kernel(const U* __restrict__ in, size_t n, unsigned long long* __restrict__ hist,
+                   uint32_t* __restrict__ partial, int xf) {
     using C = NarrowCfg<U>;
     constexpr int VEC = 16 / (int)sizeof(U);
     extern __shared__ __align__(16) uint32_t bins[];
@@ -92,40 +110,56 @@ hist_values_kernel(const U* __restrict__ in, size_t n, unsigned long long* __res
             if (c) atomicAdd(&hist[k], (unsigned long long)c);
         }
     } else {
-        for (int k = tid; k < C::NV / C::SPLIT; k += C::THREADS) {
-            const uint32_t c = bins[k];
-            if (c) atomicAdd(&hist[half * (C::NV / C::SPLIT) + k], (unsigned long long)c);
-        }
+        constexpr int HB = C::NV / C::SPLIT;
+        uint4* dst = reinterpret_cast<uint4*>(partial + (size_t)slab * C::NV + (size_t)half * HB);
+        const uint4* src = reinterpret_cast<const uint4*>(bins);
+        for (int j = tid; j < HB / 4; j += C::THREADS) dst[j] = src[j];
     }
 }
 
+// u16: hist[v] = sum over the slabs of partial[slab][v]; one thread per value, loads coalesced.
+static __global__ void __launch_bounds__(1024)
+reduce_partials_kernel(const uint32_t* __restrict__ partial, unsigned slabs, int nv, unsigned long long* __restrict__ hist) {
+    const int v = blockIdx.x * 1024 + threadIdx.x;
+    if (v >= nv) return;
+    unsigned long long c = 0;
+    for (unsigned s = 0; s < slabs; ++s) c += partial[(size_t)s * nv + v];
+    hist[v] = c;
+}
+
 // K2n: one CTA of 1024 threads; offs[v] = keys with an ordered value below v, offs[NV] = n.
+// Warp w owns the NV / 32 consecutive bins [w NV/32, (w+1) NV/32) and walks them 32 at a time
+// (coalesced loads, shuffle scan, running carry); the warps' totals meet in shared memory.
 template <int NV>
 __global__ void __launch_bounds__(1024)
 scan_values_kernel(const unsigned long long* __restrict__ hist, unsigned long long* __restrict__ offs) {
-    constexpr int PER = NV >= 1024 ? NV / 1024 : 1;
+    constexpr int PER_WARP = NV / 32;              // 8 (u8) or 2048 (u16)
+    constexpr int ROUNDS = PER_WARP >= 32 ? PER_WARP / 32 : 1;
+    constexpr int LANES = PER_WARP >= 32 ? 32 : PER_WARP;
     __shared__ unsigned long long warp_tot[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    unsigned long long local = 0;
-    if (tid * PER < NV)
-        for (int j = 0; j < PER; ++j) local += hist[tid * PER + j];
-    unsigned long long x = local;
+    const unsigned long long* h = hist + (size_t)warp * PER_WARP;
+    unsigned long long tot = 0;
+    for (int r = 0; r < ROUNDS; ++r) tot += lane < LANES ? h[r * 32 + lane] : 0ull;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const unsigned long long y = __shfl_up_sync(0xFFFFFFFFu, x, o);
-        if (lane >= o) x += y;
-    }
-    if (lane == 31) warp_tot[warp] = x;
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
+    if (lane == 0) warp_tot[warp] = tot;
     __syncthreads();
-    unsigned long long base = 0;
-    for (int w = 0; w < warp; ++w) base += warp_tot[w];
-    unsigned long long run = base + x - local;
-    if (tid * PER < NV)
-        for (int j = 0; j < PER; ++j) {
-            offs[tid * PER + j] = run;
-            run += hist[tid * PER + j];
+    unsigned long long carry = 0;
+    for (int w = 0; w < warp; ++w) carry += warp_tot[w];
+    unsigned long long* o_ = offs + (size_t)warp * PER_WARP;
+    for (int r = 0; r < ROUNDS; ++r) {
+        const unsigned long long c = lane < LANES ? h[r * 32 + lane] : 0ull;
+        unsigned long long x = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+            if (lane >= o) x += y;
         }
-    if (tid == 1023) offs[NV] = run;
+        if (lane < LANES) o_[r * 32 + lane] = carry + x - c;
+        carry += __shfl_sync(0xFFFFFFFFu, x, 31);
+    }
+    if (tid == 1023) offs[NV] = carry;
 }
 
 // K3n.  out may be the buffer the keys were read from (the histogram has consumed them).

@@ -65,15 +65,17 @@ template <> struct Variants<FAM_KEYS, 1> { static constexpr VariantDesc v[] = {{
 #define B200_NV_KEYS_2 2
 template <> struct Variants<FAM_KEYS, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0x2000}, {3, 512, 24, 2, 0}}; };
 // (lbb bits 8+ = the ABL / FEAT mask of sort_kernels.cuh: FEAT_STG = 32 -> 0x2000, FEAT_NODOM = 64 -> 0x4000)
-// Round-2 sweeps (profiles/r02_sweep_v30_v32.README.txt): st.global write-out +2.9 % on u32, neutral on u64 -> default;
+// Round-2 sweeps (profiles/r02_sweep_v30_v32.README.txt, r02_sweep_v33_stg_1B.jsonl): st.global write-out +2.9 % per middle
+// pass on u32 (default there and for the narrower widths), but on u64 the last pass loses more than the middle ones win
+// (1 B keys: 37.21 ms against 36.97) -> plain stores stay the u64 default;
 // plain-atomic scatter (FEAT_NODOM), 1024-thread tiles with one CTA per SM (-9 %), 32- and 40-register shapes with
 // 64 / 48 resident warps (-19 % / -1..8 %) all lose and are not shipped (1024x26x1, 1024x16x1, 1024x8x2, 768x10x2 ...).
 #define B200_NV_KEYS_4 6
 template <> struct Variants<FAM_KEYS, 4> { static constexpr VariantDesc v[] = {{0, 512, 26, 2, 0x2000}, {3, 512, 22, 2, 0}, {0, 512, 22, 2, 0}, {0, 512, 16, 2, 0},
     {0, 512, 26, 2, 0x6000}, {0, 512, 26, 2, 0}}; };
 #define B200_NV_KEYS_8 5
-template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0x2000}, {3, 512, 16, 2, 0}, {0, 256, 20, 3, 0},
-    {0, 512, 16, 2, 0x6000}, {0, 512, 16, 2, 0}}; };
+template <> struct Variants<FAM_KEYS, 8> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}, {3, 512, 16, 2, 0}, {0, 256, 20, 3, 0},
+    {0, 512, 16, 2, 0x6000}, {0, 512, 16, 2, 0x2000}}; };
 #define B200_NV_KEYS_16 2
 template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0x2000}, {3, 256, 12, 2, 0}}; };
 #define B200_NV_RECORDS_8 2
@@ -151,7 +153,7 @@ struct PassLauncher {
 // (the partition family always writes to a caller-named destination: no tmp region)
 //                                          ^--------- zeroed by one memset ---------------^
 struct Layout {
-    size_t tmp_off, bins_off, plan_off, hist_off, ticket_off, stats_off, lb_off, narrow_off, total;
+    size_t tmp_off, bins_off, plan_off, hist_off, ticket_off, stats_off, lb_off, narrow_off, narrow_partial_off, total;
     size_t zero_off, zero_bytes;
     int portions;
     size_t portion_elems;  // elements per portion (multiple of tile)
@@ -182,6 +184,9 @@ inline Layout make_layout(size_t n, size_t elem_bytes, int digits, int tile, boo
     L.zero_off = L.hist_off;
     L.zero_bytes = off - L.hist_off;
     L.narrow_off = off; off = align_up(off + (narrow_bins ? (2 * narrow_bins + 1) * 8 : 0), 256);
+    // u16: per-slab partial histograms (narrow_kernels.cuh), sized for the largest slab count any device gets for n
+    L.narrow_partial_off = off;
+    if (narrow_bins == 65536) off = align_up(off + (size_t)narrow_slabs16(n, 2 * NARROW_MAX_SLABS) * narrow_bins * 4, 256);
     L.total = off;
     return L;
 }

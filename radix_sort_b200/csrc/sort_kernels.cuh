@@ -65,11 +65,14 @@ __device__ __forceinline__ u128 ld_elem<u128>(const u128* p) {
 // store into global memory through the global state space (STG), not the generic one (ST):
 // the address of a run comes out of integer arithmetic, which nvcc otherwise stores through
 // the generic window check.  Peer-mapped receive buffers (K7) are global addresses too.
-__device__ __forceinline__ void st_global(unsigned long long addr, unsigned char v) { asm volatile("st.global.u8 [%0], %1;" ::"l"(addr), "r"((unsigned)v) : "memory"); }
-__device__ __forceinline__ void st_global(unsigned long long addr, unsigned short v) { asm volatile("st.global.u16 [%0], %1;" ::"l"(addr), "h"(v) : "memory"); }
-__device__ __forceinline__ void st_global(unsigned long long addr, unsigned int v) { asm volatile("st.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory"); }
-__device__ __forceinline__ void st_global(unsigned long long addr, unsigned long long v) { asm volatile("st.global.u64 [%0], %1;" ::"l"(addr), "l"(v) : "memory"); }
-__device__ __forceinline__ void st_global(unsigned long long addr, u128 v) { asm volatile("st.global.v2.u64 [%0], {%1, %2};" ::"l"(addr), "l"(v.lo), "l"(v.hi) : "memory"); }
+// No "memory" clobber: the write-out keeps its shared-memory loads of the next rows in flight
+// across these stores (with the clobber pass 0 of a u64 sort was 4 % slower); every reader of
+// the stored data is behind a barrier or a kernel boundary.
+__device__ __forceinline__ void st_global(unsigned long long addr, unsigned char v) { asm volatile("st.global.u8 [%0], %1;" ::"l"(addr), "r"((unsigned)v)); }
+__device__ __forceinline__ void st_global(unsigned long long addr, unsigned short v) { asm volatile("st.global.u16 [%0], %1;" ::"l"(addr), "h"(v)); }
+__device__ __forceinline__ void st_global(unsigned long long addr, unsigned int v) { asm volatile("st.global.u32 [%0], %1;" ::"l"(addr), "r"(v)); }
+__device__ __forceinline__ void st_global(unsigned long long addr, unsigned long long v) { asm volatile("st.global.u64 [%0], %1;" ::"l"(addr), "l"(v)); }
+__device__ __forceinline__ void st_global(unsigned long long addr, u128 v) { asm volatile("st.global.v2.u64 [%0], {%1, %2};" ::"l"(addr), "l"(v.lo), "l"(v.hi)); }
 
 // ---------------------------------------------------------------------------
 // K1: all-digit histogram.  16-byte coalesced loads (LDG.128), four in flight
@@ -795,7 +798,8 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     // ---- coalesced run write-out; key-only passes check the order of the tile
     if (ABL & 4) return false;
     if ((!Tr::NEEDS_STABLE && pass == 0) || (ABL & 2)) {
-        write_out<Tr, WORKERS, ITEMS, FULL, false, ABL>(sh, a, pp.xf_out, tile_n, tid);
+        // (FEAT_STG only pays in the verifying write-out: pass 0 is 3-4 % slower with it -- r02 sweep v33)
+        write_out<Tr, WORKERS, ITEMS, FULL, false, (ABL & ~FEAT_STG)>(sh, a, pp.xf_out, tile_n, tid);
         return false;
     }
     return write_out<Tr, WORKERS, ITEMS, FULL, true, ABL>(sh, a, pp.xf_out, tile_n, tid);
@@ -890,7 +894,7 @@ struct SmallSmem {
 
 template <typename Tr>
 __global__ void __launch_bounds__(SMALL_THREADS, 1)
-small_sort_kernel(typename Tr::elem_t* __restrict__ keys, uint32_t n, typename Tr::Params prm, int no_skip) {
+small_sort_kernel(typename Tr::elem_t* keys, uint32_t n, typename Tr::Params prm, int no_skip) {
     using E = typename Tr::elem_t;
     constexpr int ITEMS = SMALL_ITEMS;
     constexpr int WARPS = SMALL_THREADS / 32;
@@ -906,7 +910,7 @@ small_sort_kernel(typename Tr::elem_t* __restrict__ keys, uint32_t n, typename T
     E e[ITEMS];
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i)
-        if (wbase + i * 32 < n) e[i] = Tr::xform_in(ld_elem(keys + wbase + i * 32), prm);
+        if (wbase + i * 32 < n) e[i] = Tr::xform_in(keys[wbase + i * 32], prm);  // plain load: the kernel stores into the same buffer
 
     for (int pass = 0; pass < Tr::DIGITS; ++pass) {
 #pragma unroll

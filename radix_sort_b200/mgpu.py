@@ -470,7 +470,8 @@ class Communicator:
                 raise B200SortError(1, "every shard must be a contiguous tensor on its communicator device")
             if t.numel() * t.element_size() % kb:
                 raise B200SortError(1, "shard size is not a whole number of keys")
-        torch.cuda.synchronize()  # the library runs on its own streams
+        for d in sorted(set(self.devices)):  # the library reads every shard on its own streams, on every device
+            torch.cuda.synchronize(d)
         ptrs = (ctypes.c_void_p * G)(*[t.data_ptr() if t.numel() else None for t in shards])
         n_in = (ctypes.c_size_t * G)(*[t.numel() * t.element_size() // kb for t in shards])
         outs = (ctypes.c_void_p * G)()

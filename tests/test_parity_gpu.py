@@ -381,6 +381,7 @@ def test_forced_rerank_keys(kind, cuda):
     a = _ref.random_keys(kind, n, seed=5)
     want = _ref.expected_sorted(a, kind)
     rs.debug_force_rerank(True)
+    rs.debug_narrow_fill(False)  # 1- and 2-byte keys: through K3, which is what this test is about
     try:
         for variant in range(rs.num_variants(rs.key_bytes(k))):
             rs.set_variant(rs.key_bytes(k), variant)
@@ -393,11 +394,14 @@ def test_forced_rerank_keys(kind, cuda):
     finally:
         rs.set_variant(rs.key_bytes(k), -1)
         rs.debug_force_rerank(False)
-    t = _to_device(a, cuda)
-    ws = torch.empty(rs.temp_bytes(n, k), dtype=torch.uint8, device=cuda)
-    rs.radix_sort(t, k, workspace=ws)
-    torch.cuda.synchronize()
-    assert rs.debug_reranked_tiles(ws, n, k) == 0, "a tile failed its order check on the fast path"
+    try:
+        t = _to_device(a, cuda)
+        ws = torch.empty(rs.temp_bytes(n, k), dtype=torch.uint8, device=cuda)
+        rs.radix_sort(t, k, workspace=ws)
+        torch.cuda.synchronize()
+        assert rs.debug_reranked_tiles(ws, n, k) == 0, "a tile failed its order check on the fast path"
+    finally:
+        rs.debug_narrow_fill(True)
 
 
 @pytest.mark.parametrize("key_kind,dt", [("u32", np.uint32), ("f64", np.float64)])
