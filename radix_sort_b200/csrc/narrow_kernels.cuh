@@ -17,7 +17,8 @@
 //   K2n  scan_values_kernel   exclusive prefix over the bins -> offs[NV + 1]
 //   K3n  fill_values_kernel   CTA b owns output elements [b C, (b + 1) C): finds its first
 //          value by a two-level search of offs, then walks the values: short runs are
-//          written by one thread each, long runs by the whole CTA with 16-byte stores.
+//          written by one thread each, middle ones by a warp, long ones by the whole CTA,
+//          with 16-byte stores.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -163,27 +164,47 @@ scan_values_kernel(const unsigned long long* __restrict__ hist, unsigned long lo
 }
 
 // K3n.  out may be the buffer the keys were read from (the histogram has consumed them).
+// Runs of one value inside the CTA's chunk come in three sizes: short ones are written by the thread
+// that found them, middle ones by one warp each (32 lanes x 16 bytes per step; a u16 sort of 2^27
+// uniform keys is 65536 runs of 4 KB: one CTA-wide loop per run left 3/4 of the CTA idle and was 0.2 ms
+// of pure latency), long ones by the whole CTA.
+template <typename U>
+__device__ __forceinline__ void fill_run(U* __restrict__ out, unsigned long long s2, unsigned long long e2, U val, unsigned t, unsigned nt) {
+    constexpr int VEC = 16 / (int)sizeof(U);
+    const uintptr_t a0 = (uintptr_t)(out + s2);
+    unsigned long long hd = ((16 - (a0 & 15)) & 15) / sizeof(U);  // head up to 16-byte alignment, vectors, tail
+    if (hd > e2 - s2) hd = e2 - s2;
+    const unsigned long long nv = (e2 - s2 - hd) / VEC;
+    const unsigned long long tl = s2 + hd + nv * VEC;
+    for (unsigned long long i = t; i < hd; i += nt) out[s2 + i] = val;
+    const uint32_t w = sizeof(U) == 1 ? 0x01010101u * (uint32_t)val : 0x00010001u * (uint32_t)val;
+    const uint4 vv = make_uint4(w, w, w, w);
+    uint4* vp = reinterpret_cast<uint4*>(out + s2 + hd);
+    for (unsigned long long i = t; i < nv; i += nt) vp[i] = vv;
+    for (unsigned long long i = tl + t; i < e2; i += nt) out[i] = val;
+}
+
 template <typename U>
 __global__ void __launch_bounds__(1024)
 fill_values_kernel(U* __restrict__ out, size_t n, const unsigned long long* __restrict__ offs, int xf) {
     using C = NarrowCfg<U>;
     constexpr int NV = C::NV;
     constexpr int THREADS = 1024;
-    constexpr int VEC = 16 / (int)sizeof(U);
-    constexpr int LONG_RUN = 256;   // elements from which a run is written by the whole CTA
+    constexpr unsigned SHORT_RUN = 32;      // elements below which the finding thread writes the run itself
+    constexpr unsigned LONG_RUN = 32768;    // elements from which the whole CTA writes the run
     constexpr int QCAP = 1024;
     __shared__ unsigned s_first;
-    __shared__ unsigned s_qn;
-    __shared__ unsigned q_val[QCAP];
-    __shared__ unsigned long long q_lo[QCAP], q_hi[QCAP];
-    const int tid = threadIdx.x;
-    // chunk of the output, whole 16-byte vectors of the (possibly unaligned) buffer
+    __shared__ unsigned s_qn[2];            // [0] warp-sized runs, [1] CTA-sized runs
+    __shared__ unsigned q_val[2][QCAP];
+    __shared__ unsigned long long q_lo[2][QCAP], q_hi[2][QCAP];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // chunk of the output: whole 4096-element granules
     const size_t chunk = ((n + gridDim.x - 1) / gridDim.x + 4095) / 4096 * 4096;
     const size_t lo = (size_t)blockIdx.x * chunk;
     if (lo >= n) return;
     const size_t hi = lo + chunk < n ? lo + chunk : n;
-    // first value of the chunk: the largest v with offs[v] <= lo.  Level 1: 1024 probes NV / 1024 apart
-    // (the last one that passes is found with a ballot per warp + one shared word), level 2: the bracket.
+    // first value of the chunk: the largest v with offs[v] <= lo.  Level 1: 1024 probes NV / 1024 apart,
+    // level 2: the bracket the last passing probe opens.
     if (tid == 0) s_first = 0;
     __syncthreads();
     constexpr int STRIDE = NV >= THREADS ? NV / THREADS : 1;
@@ -197,7 +218,7 @@ fill_values_kernel(U* __restrict__ out, size_t n, const unsigned long long* __re
     }
     unsigned vcur = s_first;
     for (;;) {
-        if (tid == 0) s_qn = 0;
+        if (tid < 2) s_qn[tid] = 0;
         __syncthreads();
         const unsigned v = vcur + (unsigned)tid;
         unsigned long long s = 0, e = 0;
@@ -207,39 +228,25 @@ fill_values_kernel(U* __restrict__ out, size_t n, const unsigned long long* __re
             if (s < lo) s = lo;
             if (e > hi) e = hi;
         }
-        const bool any = v < (unsigned)NV && e > s;
-        if (any) {
+        if (v < (unsigned)NV && e > s) {
             const U val = from_ordered_rt<U>((U)v, xf);
-            if (e - s < (unsigned long long)LONG_RUN) {
+            if (e - s < SHORT_RUN) {
                 for (unsigned long long p = s; p < e; ++p) out[p] = val;
             } else {
-                const unsigned slot = atomicAdd(&s_qn, 1u);
-                q_val[slot] = val;
-                q_lo[slot] = s;
-                q_hi[slot] = e;
+                const int q = e - s >= LONG_RUN ? 1 : 0;
+                const unsigned slot = atomicAdd(&s_qn[q], 1u);
+                q_val[q][slot] = val;
+                q_lo[q][slot] = s;
+                q_hi[q][slot] = e;
             }
         }
         // done when the last value of this batch already ends at or past the chunk's end
         const unsigned vlast = vcur + THREADS - 1 < (unsigned)NV - 1 ? vcur + THREADS - 1 : (unsigned)NV - 1;
         const bool done = offs[vlast + 1] >= hi || vcur + THREADS >= (unsigned)NV;
         __syncthreads();
-        const unsigned qn = s_qn;
-        for (unsigned k = 0; k < qn; ++k) {
-            const U val = (U)q_val[k];
-            const unsigned long long s2 = q_lo[k], e2 = q_hi[k];
-            // head up to 16-byte alignment, vectors, tail
-            const uintptr_t a0 = (uintptr_t)(out + s2);
-            unsigned long long hd = ((16 - (a0 & 15)) & 15) / sizeof(U);
-            if (hd > e2 - s2) hd = e2 - s2;
-            const unsigned long long nv = (e2 - s2 - hd) / VEC;
-            const unsigned long long tl = s2 + hd + nv * VEC;
-            if ((unsigned long long)tid < hd) out[s2 + tid] = val;
-            uint32_t w = sizeof(U) == 1 ? 0x01010101u * (uint32_t)val : 0x00010001u * (uint32_t)val;
-            const uint4 vv = make_uint4(w, w, w, w);
-            uint4* vp = reinterpret_cast<uint4*>(out + s2 + hd);
-            for (unsigned long long i = tid; i < nv; i += THREADS) vp[i] = vv;
-            if (tl + tid < e2) out[tl + tid] = val;
-        }
+        const unsigned qw = s_qn[0], qc = s_qn[1];
+        for (unsigned k = warp; k < qw; k += THREADS / 32) fill_run<U>(out, q_lo[0][k], q_hi[0][k], (U)q_val[0][k], lane, 32);
+        for (unsigned k = 0; k < qc; ++k) fill_run<U>(out, q_lo[1][k], q_hi[1][k], (U)q_val[1][k], tid, THREADS);
         if (done) return;
         vcur += THREADS;
         __syncthreads();
