@@ -228,6 +228,22 @@ int b200sort_partition_count_device(const void *d_in, void *d_tmp, size_t tmp_by
 int b200sort_partition_exchange_device(const void *d_in, void *d_tmp, size_t tmp_bytes, size_t n, int kind,
                                        const void *splitters, int nsplit, void *const *peer_bases,
                                        const uint64_t *d_peer_offsets, void *stream);
+/* K7 with no count phase at all: one read of d_in, every tile CLAIMS room for its keys of
+ * bucket r with one system-scope atomicAdd on the u64 cursor at device address cursor_addrs[r]
+ * (on this GPU or, peer-mapped, on bucket r's owner) and stores them at region_bases[r] + the
+ * claimed element offset.  The order of the keys inside a region is unspecified (the region is
+ * sorted next; equal keys are bit-identical).  region_caps[r] = elements the region holds: a
+ * claim that would pass it is not stored and sets bit r of *d_flags; the cursor counts it all
+ * the same, so after the call (and a barrier over all writers) a cursor holds the true size of
+ * its bucket.  Cursors and *d_flags must be zero before the first writer starts.  No counts
+ * travel, no all_gather, no second read of the shard.  splitters / region_bases /
+ * cursor_addrs / region_caps: host arrays (nsplit, nsplit + 1, ...).  Workspace:
+ * b200sort_temp_bytes(n, kind). */
+int b200sort_partition_claim_device(const void *d_in, void *d_tmp, size_t tmp_bytes, size_t n, int kind,
+                                    const void *splitters, int nsplit, void *const *region_bases,
+                                    const uint64_t *cursor_addrs, const uint64_t *region_caps,
+                                    uint32_t *d_flags, void *stream);
+
 /* Step 3 in pieces, so that the receiver can start sorting the buckets of one
  * piece while the next piece is still crossing NVLink: stores only the buckets
  * whose bit is set in bucket_mask (bit r = bucket r); the other keys are read

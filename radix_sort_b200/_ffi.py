@@ -40,6 +40,8 @@ PROTOTYPES = {
                                                 c_void_p, c_void_p]),
     "b200sort_partition_exchange_device": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_int, c_void_p, c_int,
                                                    c_void_p, c_void_p, c_void_p]),
+    "b200sort_partition_claim_device": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_int, c_void_p, c_int, c_void_p, c_void_p,
+                                                c_void_p, c_void_p, c_void_p]),
     "b200sort_debug_force_rerank": (None, [c_int]),
     "b200sort_debug_small_sort": (None, [c_int]),
     "b200sort_debug_narrow_fill": (None, [c_int]),

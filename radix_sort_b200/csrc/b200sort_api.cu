@@ -597,6 +597,27 @@ int b200sort_partition_exchange_device(const void* d_in, void* d_tmp, size_t tmp
                            peer_bases, d_peer_offsets, stream);
 }
 
+int b200sort_partition_claim_device(const void* d_in, void* d_tmp, size_t tmp_bytes, size_t n, int kind, const void* splitters,
+                                    int nsplit, void* const* region_bases, const uint64_t* cursor_addrs,
+                                    const uint64_t* region_caps, uint32_t* d_flags, void* stream) {
+    if (nsplit < 0 || nsplit > MAX_SPLITTERS) return fail(B200SORT_ERR_INVALID_ARG, "nsplit must be in [0, 15]");
+    if (nsplit > 0 && !splitters) return fail(B200SORT_ERR_INVALID_ARG, "null splitters");
+    if (n && !d_in) return fail(B200SORT_ERR_INVALID_ARG, "null device pointer");
+    if (!region_bases || !cursor_addrs || !region_caps || !d_flags) return fail(B200SORT_ERR_INVALID_ARG, "null claim argument");
+    const size_t kb = b200sort_key_bytes(kind);
+    if (kb == 0) return fail(B200SORT_ERR_UNSUPPORTED_KIND, "unknown key kind " + std::to_string(kind));
+    SortCall c;
+    c.elems = const_cast<void*>(d_in); c.ws = d_tmp; c.ws_bytes = tmp_bytes; c.n = n;
+    c.alt_out = region_bases[0];
+    c.st = static_cast<cudaStream_t>(stream); c.flags = B200SORT_FLAG_NO_SKIP; c.xf = kind_xf(kind);
+    c.splitters = splitters; c.nsplit = nsplit; c.phase = SortCall::PHASE_CLAIM;
+    c.peer_bases = region_bases;
+    c.claim_cursors = reinterpret_cast<const unsigned long long*>(cursor_addrs);
+    c.claim_caps = reinterpret_cast<const unsigned long long*>(region_caps);
+    c.claim_flags = d_flags;
+    return front_by_width<FAM_PARTITION>(kb, c);
+}
+
 int b200sort_partition_exchange_part_device(const void* d_in, void* d_tmp, size_t tmp_bytes, size_t n, int kind,
                                             const void* splitters, int nsplit, void* const* peer_bases,
                                             const uint64_t* d_peer_offsets, unsigned bucket_mask, int again, void* stream) {

@@ -62,6 +62,17 @@ int make_params(const SortCall& c, typename FamilyTraits<FAM, W>::type::Params* 
                     return fail(B200SORT_ERR_INVALID_ARG, "peer buffer null or not aligned to the element size");
                 p.peer[j] = (unsigned long long)(uintptr_t)c.peer_bases[j];
             }
+        if (c.phase == SortCall::PHASE_CLAIM) {
+            if (!c.peer_bases || !c.claim_cursors || !c.claim_caps || !c.claim_flags)
+                return fail(B200SORT_ERR_INVALID_ARG, "claim phase needs region bases, cursors, capacities and a flag word");
+            p.claim = 1u;
+            for (int j = 0; j <= c.nsplit; ++j) {
+                if (!c.claim_cursors[j] || (c.claim_cursors[j] & 7)) return fail(B200SORT_ERR_INVALID_ARG, "cursor null or not 8-byte aligned");
+                p.cursor[j] = c.claim_cursors[j];
+                p.cap[j] = c.claim_caps[j];
+            }
+            p.flags = (unsigned long long)(uintptr_t)c.claim_flags;
+        }
     }
     *prm = p;
     return B200SORT_OK;
@@ -82,7 +93,8 @@ int sort_front(const SortCall& c) {
     const bool do_hist = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_COUNT;
     const bool do_zero = do_hist || (ph == SortCall::PHASE_SCATTER && c.rezero);
     const bool do_plan = do_hist;
-    const bool do_scatter = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_SCATTER;
+    const bool claim = ph == SortCall::PHASE_CLAIM;
+    const bool do_scatter = ph == SortCall::PHASE_ALL || ph == SortCall::PHASE_SCATTER || claim;
     const bool do_count = do_plan;  // the call that delivers the counts
     if (n == 0) {
         if (c.hist_copy && do_count) B200_CU(cudaMemsetAsync(c.hist_copy, 0, (size_t)c.hist_copy_words * 8, st));
@@ -186,6 +198,10 @@ int sort_front(const SortCall& c) {
     PhaseTimer timer(c.out_ms != nullptr, st);
     timer.mark();
     if (do_zero) B200_CU(cudaMemsetAsync(ws + L.zero_off, 0, L.zero_bytes, st));
+    if (claim) {  // no histogram, no plan kernel, no look-back: an all-zero plan (pass 0 executes, reads the input) and fresh tickets
+        B200_CU(cudaMemsetAsync(ws + L.plan_off, 0, sizeof(Plan), st));
+        B200_CU(cudaMemsetAsync(ws + L.ticket_off, 0, L.lb_off - L.ticket_off, st));
+    }
 
     // K1: one read, all digit histograms
     if (do_hist) {
@@ -227,7 +243,7 @@ int sort_front(const SortCall& c) {
     timer.mark();
     if (!do_scatter) return B200SORT_OK;
     // fused exchange: bucket r starts at element peer_offsets[r] of rank r's receive buffer
-    if (c.peer_offsets)
+    if (c.peer_offsets && !claim)
         B200_CU(cudaMemcpyAsync(bins, c.peer_offsets, (size_t)(c.nsplit + 1) * 8, cudaMemcpyDeviceToDevice, st));
 
     // K3: one launch per digit per portion

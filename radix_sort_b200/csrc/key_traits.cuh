@@ -192,6 +192,16 @@ struct PartitionTraits {
         // buckets this launch writes out (bit r = bucket r); the others are ranked but not
         // stored -- the overlapped multi-GPU exchange sends the buckets in two launches
         unsigned mask;
+        // claim mode (claim != 0): no counts are known in advance and no look-back runs.  Every tile
+        // claims room for its keys of bucket r with ONE system-scope atomicAdd on the cursor of that
+        // bucket's region -- cursor[r], a u64 that may live on another GPU -- and stores them at
+        // peer[r] + old value (the order inside a region is free: it is sorted next).  A claim that
+        // would pass cap[r] elements is not stored and sets bit r of *flags (the caller then takes
+        // the exact path); the cursor still counts it, so its final value is the bucket's true size.
+        unsigned claim;
+        unsigned long long cursor[MAX_SPLITTERS + 1];
+        unsigned long long cap[MAX_SPLITTERS + 1];
+        unsigned long long flags;
     };
     __device__ __forceinline__ static bool prefix_less(elem_t, elem_t, int, const Params&) { return false; }
     __device__ __forceinline__ static elem_t xform_in(elem_t e, const Params&) { return e; }

@@ -228,7 +228,12 @@ struct SortCall {
     //   PHASE_SCATTER K3 only, on the state PHASE_COUNT left in the same ws; bucket r goes to
     //                 peer_bases[r] (peer memory) starting at element peer_offsets[r]
     //   PHASE_READ_STATS: no kernel; synchronises and copies the workspace's counter of re-ranked tiles to *out_stats
-    enum { PHASE_ALL = 0, PHASE_COUNT = 1, PHASE_SCATTER = 2, PHASE_READ_STATS = 6 };
+    //   PHASE_CLAIM   K3 only, no counts at all: every tile claims room in its buckets' regions with an atomic on
+    //                 claim_cursors[r] (device addresses, possibly on peers) -- PartitionTraits::Params::claim
+    enum { PHASE_ALL = 0, PHASE_COUNT = 1, PHASE_SCATTER = 2, PHASE_CLAIM = 3, PHASE_READ_STATS = 6 };
+    const unsigned long long* claim_cursors = nullptr;  // host array, nsplit + 1 device addresses of u64 cursors
+    const unsigned long long* claim_caps = nullptr;     // host array, nsplit + 1 region capacities (elements)
+    void* claim_flags = nullptr;                        // device u32: bit r set when bucket r did not fit
     unsigned* out_stats = nullptr;
     int phase = PHASE_ALL;
     unsigned bucket_mask = 0xFFFFFFFFu;              // PHASE_SCATTER: buckets this launch stores (bit r = bucket r)

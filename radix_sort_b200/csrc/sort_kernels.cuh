@@ -480,6 +480,7 @@ __device__ __forceinline__ bool write_out(const PassShared<Tr, THREADS, ITEMS>& 
             if (!((a.prm.mask >> b) & 1u)) continue;
             const uint32_t lo = sh.excl[b], hi = lo + sh.cnt[b];
             const unsigned long long base = sh.gptr[b];
+            if (base == 0) continue;  // claim mode: the region is full (the caller falls back)
             for (uint32_t idx = lo + tid; idx < hi; idx += THREADS)
                 st_elem<E>(base + (unsigned long long)idx * sizeof(E), sh.tile[idx], STG);
         }
@@ -636,6 +637,21 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
             const uint32_t cnt_d = sh.cnt[d];
             const unsigned long long bin_d = a.bins_in[d];  // asked for before the walk: its round trip overlaps the walk's
             unsigned long long excl_tiles = 0;
+            if constexpr (Tr::FEW_BUCKETS) {
+                if (a.prm.claim) {
+                    unsigned long long base = 0;
+                    if (d <= a.prm.nsplit && cnt_d != 0 && ((a.prm.mask >> d) & 1u)) {
+                        const unsigned long long old =
+                            atomicAdd_system(reinterpret_cast<unsigned long long*>(a.prm.cursor[d]), (unsigned long long)cnt_d);
+                        if (old + cnt_d <= a.prm.cap[d])
+                            base = Tr::dst_base((unsigned)d, dst, a.prm) + old * sizeof(E) - (unsigned long long)sh.excl[d] * sizeof(E);
+                        else
+                            atomicOr(reinterpret_cast<unsigned*>(a.prm.flags), 1u << d);
+                    }
+                    sh.gptr[d] = base;
+                    return;
+                }
+            }
             if (ABL & 1) {  // timing ablation: no polling, a plausible distinct address
                 excl_tiles = min((unsigned long long)tile * (WORKERS * ITEMS / RADIX),
                                  (unsigned long long)a.portion_n - cnt_d - min((unsigned long long)a.portion_n - cnt_d, bin_d));
@@ -657,7 +673,9 @@ __device__ __forceinline__ bool rank_and_scatter(const PassShared<Tr, WORKERS, I
     uint32_t count = 0;
     if (tid < RADIX) {
         count = column_total<WARPS>(sh.warp_hist, tid);
-        st_relaxed_u32(lb + tid, (tile == 0 ? LB_FLAG_INCLUSIVE : LB_FLAG_PARTIAL) | count);
+        bool publish = true;
+        if constexpr (Tr::FEW_BUCKETS) publish = !a.prm.claim;  // claim mode: nobody looks back
+        if (publish) st_relaxed_u32(lb + tid, (tile == 0 ? LB_FLAG_INCLUSIVE : LB_FLAG_PARTIAL) | count);
         // the same tile's words in the other half: nobody reads them before the next launch
         if (a.lookback_half) a.lookback[(pp.src_is_tmp ? 0 : a.lookback_half) + (size_t)tile * RADIX + tid] = 0u;
         sh.cnt[tid] = count;

@@ -31,6 +31,19 @@ Fused form (`sort_sharded(..., exchange=PeerExchange(...))`): steps 3-5 become
 so the keys cross NVLink inside the partition kernel's write-out and are never
 staged in a send buffer or copied by a separate collective.
 
+Claim form (the default whenever the exchange has a control block, round 2): no count
+phase and no count all_gather at all --
+    3*. b200sort_partition_claim_device  one read of the shard; every K7 tile claims
+        room in the destination's receive buffer with ONE system-scope atomicAdd on a
+        cursor that lives on the destination GPU, and stores its keys there (the order
+        inside a destination is free: it is sorted next)
+    4*. barrier; the cursors now hold every rank's receive count
+and, with `staged=True`, every rank's range is cut in two by one more splitter: the
+FIRST halves travel inside K7 as above, the SECOND halves are claimed into a local
+staging buffer (one region per destination) and cross NVLink afterwards on the copy
+engines (cudaMemcpyAsync on a side stream) WHILE every rank already sorts its first
+half -- the exchange of half of the bytes costs no SM time and no wall time.
+
 The device steps go through an `ops` object so that the host-side logic (sample
 positions, splitter choice, count exchange, offsets) runs under gloo on CPU in
 tests/ with a numpy test double; the default ops are the CUDA C ABI and fail
@@ -111,7 +124,10 @@ class PeerExchange:
     stream after whatever consumed the previous result; consume the result on
     the stream sort_sharded ran on (or synchronise with it) before the next call."""
 
-    def __init__(self, capacity_keys: int, key_bytes: int, device, group=None):
+    CTRL_BYTES = 512  # per rank, behind the receive area: [0] cursor of the receive buffer, [1..16] cursors of the
+                      # staging regions (one per destination), [32] overflow flags (u32) -- int64 words
+
+    def __init__(self, capacity_keys: int, key_bytes: int, device, group=None, staging: bool = True):
         import torch
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
@@ -120,10 +136,34 @@ class PeerExchange:
         self.capacity = int(capacity_keys)
         self.key_bytes = int(key_bytes)
         self.group = group if group is not None else dist.group.WORLD
-        self.buf = symm.empty(self.capacity * self.key_bytes, dtype=torch.uint8, device=device)
+        self.world = dist.get_world_size(self.group)
+        self.recv_bytes = (self.capacity * self.key_bytes + 255) // 256 * 256
+        self.buf = symm.empty(self.recv_bytes + self.CTRL_BYTES, dtype=torch.uint8, device=device)
         self.handle = symm.rendezvous(self.buf, self.group)
         self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
-        self.recv_rows = self.buf.view(self.capacity, self.key_bytes)
+        self.recv_rows = self.buf[: self.capacity * self.key_bytes].view(self.capacity, self.key_bytes)
+        self.ctrl = self.buf[self.recv_bytes:].view(torch.int64)      # this rank's control block
+        self.ctrl.zero_()
+        # staging buffer of the second halves: one region per destination rank (plain device memory)
+        self.stage_cap = self.capacity // max(1, self.world) if staging else 0
+        self.stage = (torch.empty(self.world * self.stage_cap * self.key_bytes, dtype=torch.uint8, device=device)
+                      if staging and self.stage_cap else None)
+        self._peer_views = {}
+        torch.cuda.synchronize(device)
+        self.handle.barrier(channel=0)  # every rank's cursors are zero before anybody claims
+
+    def cursor_addr(self, rank: int, word: int = 0) -> int:
+        """device address (in this process) of control word `word` of `rank`"""
+        return self.peer_ptrs[rank] + self.recv_bytes + 8 * word
+
+    def peer_rows(self, rank: int):
+        """rank's receive buffer as a (capacity, key_bytes) uint8 tensor of THIS process (peer memory)"""
+        import torch
+        v = self._peer_views.get(rank)
+        if v is None:
+            v = self.handle.get_buffer(rank, (self.capacity * self.key_bytes,), torch.uint8, 0).view(self.capacity, self.key_bytes)
+            self._peer_views[rank] = v
+        return v
 
     def barrier(self, channel: int = 0):
         """Device-side barrier on the current stream: every rank's stores into
@@ -220,6 +260,74 @@ class CudaOps:
                                                                self._stream()))
         workspace.record_stream(self.torch.cuda.current_stream(self.device))
         exchange.barrier(channel)
+
+    def partition_claim(self, rows, kind: Kind, splitters_host: np.ndarray, workspace, exchange, staged: bool):
+        """K7 in claim mode (b200sort_partition_claim_device).  staged=False: bucket r is rank r's range, stored
+        into rank r's receive buffer.  staged=True: 2 * world buckets, bucket 2 d -> rank d's receive buffer,
+        bucket 2 d + 1 -> region d of the local staging buffer."""
+        n = rows.shape[0]
+        nsplit = int(splitters_host.shape[0])
+        spl = np.ascontiguousarray(splitters_host)
+        nb = nsplit + 1
+        me = exchange.handle.rank
+        kb = exchange.key_bytes
+        if staged:
+            stage0 = exchange.stage.data_ptr()
+            bases = [exchange.peer_ptrs[j // 2] if j % 2 == 0 else stage0 + (j // 2) * exchange.stage_cap * kb for j in range(nb)]
+            cursors = [exchange.cursor_addr(j // 2, 0) if j % 2 == 0 else exchange.cursor_addr(me, 1 + j // 2) for j in range(nb)]
+            caps = [exchange.capacity if j % 2 == 0 else exchange.stage_cap for j in range(nb)]
+        else:
+            bases = [exchange.peer_ptrs[j] for j in range(nb)]
+            cursors = [exchange.cursor_addr(j, 0) for j in range(nb)]
+            caps = [exchange.capacity] * nb
+        c_bases = (ctypes.c_void_p * nb)(*bases)
+        c_cur = (ctypes.c_uint64 * nb)(*cursors)
+        c_cap = (ctypes.c_uint64 * nb)(*caps)
+        flags = ctypes.c_void_p(exchange.cursor_addr(me, 32))
+        check(self.lib.b200sort_partition_claim_device(rows.data_ptr(), workspace.data_ptr(), workspace.numel(), n, int(kind),
+                                                       spl.ctypes.data if nsplit else None, nsplit, c_bases, c_cur, c_cap, flags,
+                                                       self._stream()))
+        workspace.record_stream(self.torch.cuda.current_stream(self.device))
+
+    def device_splitters(self, rows, kind: Kind, samples: int, seed: int, rank: int, world: int, parts: int, group):
+        """`parts - 1` quantiles of a global sample, picked on the device: ONE all_gather of a fixed-size block
+        (samples + their count), one sort, one tiny copy to the host.  Ranks with fewer than `samples` keys pad
+        with the largest key of the kind's order; the pads sort behind every real key and the quantile indices
+        are taken over the real ones only.  Returns ((parts - 1, key_bytes) uint8 host array, total samples)."""
+        import torch.distributed as dist
+        torch = self.torch
+        kb = rows.shape[1]
+        n_local = int(rows.shape[0])
+        key = (n_local, samples, seed, rank)
+        cache = getattr(self, "_pos_cache", None)
+        if cache is None or cache[0] != key:
+            pos = sample_positions(n_local, min(samples, n_local) if n_local else 0, seed, rank)
+            idx = torch.from_numpy(pos).to(self.device)
+            self._pos_cache = cache = (key, idx)
+        idx = cache[1]
+        m = int(idx.shape[0])
+        # block = samples rows (pads behind the real ones) + 8 bytes holding the number of real rows
+        flat = torch.empty(samples * kb + 8, dtype=torch.uint8, device=self.device)
+        body = flat[: samples * kb].view(samples, kb)
+        if m < samples:
+            pad = np.full(kb, 0xFF, dtype=np.uint8)
+            if kind in (Kind.I8, Kind.I16, Kind.I32, Kind.I64, Kind.I128, Kind.F32, Kind.F64):
+                pad[kb - 1] = 0x7F  # little-endian: the largest signed value / the positive NaN with the largest payload
+            body[m:] = torch.from_numpy(pad).to(self.device)
+        if m:
+            body[:m] = rows[idx]
+        flat[samples * kb:] = torch.tensor([m], dtype=torch.int64).view(torch.uint8).to(self.device)
+        allb = torch.empty((world, samples * kb + 8), dtype=torch.uint8, device=self.device)
+        dist.all_gather_into_tensor(allb, flat, group=group)
+        total = allb[:, samples * kb:].contiguous().view(torch.int64).sum()
+        pool = allb[:, : samples * kb].reshape(world * samples, kb).contiguous()
+        self.local_sort(pool, kind)
+        j = torch.arange(1, parts, dtype=torch.int64, device=self.device)
+        pick_idx = torch.clamp((total * j) // parts, max=max(world * samples - 1, 0))
+        picks = pool[pick_idx]
+        packed = torch.cat([picks.reshape(-1), total.reshape(1).view(torch.uint8)]).cpu().numpy()
+        tot = int(packed[-8:].view(np.int64)[0])
+        return np.ascontiguousarray(packed[:-8].reshape(parts - 1, kb)), tot
 
     def side_stream(self):
         """A second stream (created once) for the piece of the exchange that overlaps the first local sort."""
