@@ -85,6 +85,36 @@ int b200sort_keys_device(void *d_keys, void *d_tmp, size_t tmp_bytes, size_t n,
 int b200sort_keys_device_ex(void *d_keys, void *d_tmp, size_t tmp_bytes, size_t n,
                             int kind, void *stream, unsigned flags);
 
+/* The same device-resident sort for callers that have no way to provide d_tmp.
+ * (No counterpart in the reference: it sorts host slices and takes its temp buffer from
+ * the Rust allocator, mod.rs:71-83; this exists only because of how GPU hosts are built.)
+ *
+ * Who that is: a host that binds nothing but this library and is handed device pointers
+ * by someone else (the Rust shim links libb200sort.so only -- it has no cudaMalloc to
+ * call); a plugin living inside a process whose own allocator has already taken nearly
+ * all of HBM, where a cudaMalloc from a guest library fails or steals from the owner's
+ * budget; and loops that cannot tolerate the device-wide synchronisation that
+ * cudaMalloc / cudaFree imply.  For them the workspace is a fixed array inside the
+ * library image: B200SORT_NOALLOC_SCRATCH_BYTES of HBM on every GPU that loads the
+ * library, held until the process exits, whether or not this entry point is ever called.
+ *
+ * Sorts d_keys[0..n) in place like b200sort_keys_device, asynchronously on `stream`, on
+ * the device that is current in the calling thread.  The call itself never allocates or
+ * frees device memory, neither directly nor through a library routine.
+ * Limit: b200sort_temp_bytes(n, kind) <= B200SORT_NOALLOC_SCRATCH_BYTES (about 1.0 M
+ * 16-byte, 2.0 M 8-byte, 3.9 M 4-byte, 1.5 M 2-byte keys); anything larger is refused with
+ * B200SORT_ERR_INVALID_ARG and a message naming both numbers -- nothing is launched.
+ * The first call on each device looks up the array's device address
+ * (cudaGetSymbolAddress, once per device, cached); make that first call outside any
+ * stream capture.
+ * The array is shared by every call on that device and keeps whatever the previous sort
+ * left in it; each sort re-zeroes the counters it depends on, so back-to-back calls on
+ * one stream are fine.  Two calls whose kernels can overlap on the GPU (different
+ * streams without an event between them, or different host threads) race on the array
+ * and give garbage: order them yourself. */
+#define B200SORT_NOALLOC_SCRATCH_BYTES (16u << 20) /* 16 MiB */
+int b200sort_keys_device_noalloc(void *d_keys, size_t n, int kind, void *stream);
+
 /* Drop-in for `slice.radix_sort()` on a host slice (call sites
  * tests.rs:30,...,166; main.rs:33): copies keys to the current device, sorts,
  * copies back into `keys`, blocks until done.  Owns its device memory. */

@@ -438,6 +438,40 @@ int keys_host_pipelined(void* host, size_t n, int kind) {
 
 }  // namespace
 
+// ---- workspace inside the library image (b200sort_keys_device_noalloc) ------------------
+// Some hosts cannot hand us a d_tmp: they bind this library only (no cudaMalloc of their own), or they live
+// in a process whose allocator owns all of HBM.  For them the K1/K2/K3 workspace is this array: part of the
+// module, so it exists on every device from the moment the library's kernels are loaded there and costs
+// B200SORT_NOALLOC_SCRATCH_BYTES of HBM per device until exit.
+// In HOST code the name below is only a handle for the runtime, not a device address: handing it to a kernel
+// would fault (or quietly hit host memory where the GPU can reach it).  The address a kernel may use comes
+// from cudaGetSymbolAddress, asked once per device with that device current, and cached.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B200SORT_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_addr[NOALLOC_MAX_DEVICES] = {};  // device address of g_noalloc_scratch on device i; null = not looked up yet
+
+// Device address of the scratch array on the calling thread's current device.
+int noalloc_scratch_address(void** out) {
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES)
+        return fail(B200SORT_ERR_INVALID_ARG, "device ordinal " + std::to_string(dev) + " outside the static-scratch table");
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_addr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);  // current device == dev
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(static scratch)");
+        if (!p || ((uintptr_t)p % 256) != 0) return fail(B200SORT_ERR_CUDA, "static scratch has no usable device address");
+        g_noalloc_addr[dev] = p;
+    }
+    *out = g_noalloc_addr[dev];
+    return B200SORT_OK;
+}
+}  // namespace
+
 // ---- exported C ABI ------------------------------------------------------------------
 extern "C" {
 
@@ -475,6 +509,30 @@ int b200sort_keys_device_timed(void* d_keys, void* d_tmp, size_t tmp_bytes, size
                                unsigned flags, float* out_ms, int out_len) {
     if (!out_ms) return fail(B200SORT_ERR_INVALID_ARG, "out_ms is null");
     return keys_device_dispatch(d_keys, d_tmp, tmp_bytes, n, kind, static_cast<cudaStream_t>(stream), flags, out_ms, out_len);
+}
+
+// Device-resident sort with the workspace in g_noalloc_scratch: for callers that cannot allocate (see the
+// header).  Same launch sequence as b200sort_keys_device -- only where d_tmp comes from differs -- and no
+// cudaMalloc / cudaFree / allocating library call on this path.  The scratch is shared and dirty from the last
+// call; the sort's own memset of its counters (front_def.cuh, do_zero) is what makes that harmless, and calls
+// that overlap on the GPU race on it.
+int b200sort_keys_device_noalloc(void* d_keys, size_t n, int kind, void* stream) {
+    const size_t kb = b200sort_key_bytes(kind);
+    if (kb == 0) return fail(B200SORT_ERR_UNSUPPORTED_KIND, "unknown key kind " + std::to_string(kind));
+    if (n == 0) return B200SORT_OK;
+    if (!d_keys) return fail(B200SORT_ERR_INVALID_ARG, "null device pointer");
+    // refuse before touching the device: the layout grows with n, and n * kb alone may already overflow the array
+    const size_t limit = B200SORT_NOALLOC_SCRATCH_BYTES;
+    const size_t need = n > limit ? (size_t)-1 : b200sort_temp_bytes(n, kind);
+    if (need > limit)
+        return fail(B200SORT_ERR_INVALID_ARG,
+                    "b200sort_keys_device_noalloc: " + std::to_string(n) + " keys of " + std::to_string(kb) + " bytes need " +
+                        (n > limit ? std::string("more than ") + std::to_string(limit) : std::to_string(need)) +
+                        " bytes of workspace, the built-in scratch holds " + std::to_string(limit) +
+                        " (B200SORT_NOALLOC_SCRATCH_BYTES); use b200sort_keys_device with your own workspace");
+    void* ws = nullptr;
+    if (int rc = noalloc_scratch_address(&ws)) return rc;
+    return keys_device_dispatch(d_keys, ws, limit, n, kind, static_cast<cudaStream_t>(stream), 0, nullptr, 0);
 }
 
 int b200sort_keys_host(void* keys, size_t n, int kind) {
