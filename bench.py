@@ -228,7 +228,7 @@ def timed_sorts(rs, torch, keys, pristine, K, ws, steps: int, warm: int = 1):
     return total / steps
 
 
-def other_configs(rs, torch, np, distr, verify, _ffi, dev, buf_a, buf_b, ws, peak, steps: int, with_cpu: bool):
+def other_configs(rs, torch, np, distr, verify, _ffi, dev, buf_a, buf_b, ws, peak, steps: int, with_cpu: bool, note_error, failed):
     """BASELINE.json configs C1, C3, C4 and the demo's record shapes at their stated sizes, on one GPU.
     buf_a / buf_b: two 8 GB device buffers (uint8), reused for every case."""
     out = {}
@@ -260,70 +260,95 @@ def other_configs(rs, torch, np, distr, verify, _ffi, dev, buf_a, buf_b, ws, pea
                 "pass_frac_of_peak": round(2.0 * n * kb / (sum(executed) / len(executed)) / 1e6 / peak, 4) if executed else None,
                 "verified": True}
 
+    def case(name, *a):
+        """one configuration; a failure is recorded under its own name and the others still run"""
+        try:
+            out[name] = run_case(*a)
+        except BaseException as e:  # noqa: BLE001
+            note_error(f"other_configs/{name}", e)
+            out[name] = {"error": f"{type(e).__name__}: {e}"[:200], "verified": False}
+            if isinstance(e, (SystemExit, AssertionError)):
+                failed.append(name)
+
     D = distr.Distr
     # C1: 10 M uniform u32 (L2-resident: 40 MB + 40 MB temp; launch-latency bound, no HBM fraction claimed)
-    c1 = run_case("u32", 10_000_000, D.UNIFORM, 0.0, 0xB2000001, "C1")
-    c1.pop("pass_frac_of_peak")
-    c1["note"] = "device-resident; 80 MB working set sits in the 126 MB L2"
-    host = np.asarray(distr.uniform_host(10_000_000, rs.Kind.U32, seed=0xB2000001))
-    work = host.copy()
-    best = None
-    for _ in range(4):
-        np.copyto(work, host)
-        t0 = time.perf_counter()
-        _ffi.check(_ffi.lib().b200sort_keys_host(work.ctypes.data, work.size, int(rs.Kind.U32)))
-        dt = time.perf_counter() - t0
-        best = dt if best is None else min(best, dt)
-    assert bool(np.all(work[1:] >= work[:-1]))
-    c1["host_call_ms"] = round(best * 1e3, 3)
-    c1["host_call_note"] = "b200sort_keys_host on a pageable numpy array (what a Rust Vec is), copies inside, best of 3 after a warm-up"
-    out["C1_10M_u32"] = c1
+    try:
+        c1 = run_case("u32", 10_000_000, D.UNIFORM, 0.0, 0xB2000001, "C1")
+        c1.pop("pass_frac_of_peak")
+        c1["note"] = "device-resident; 80 MB working set sits in the 126 MB L2"
+        host = np.asarray(distr.uniform_host(10_000_000, rs.Kind.U32, seed=0xB2000001))
+        work = host.copy()
+        best = None
+        for _ in range(4):
+            np.copyto(work, host)
+            t0 = time.perf_counter()
+            _ffi.check(_ffi.lib().b200sort_keys_host(work.ctypes.data, work.size, int(rs.Kind.U32)))
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        assert bool(np.all(work[1:] >= work[:-1]))
+        c1["host_call_ms"] = round(best * 1e3, 3)
+        c1["host_call_note"] = "b200sort_keys_host on a pageable numpy array (what a Rust Vec is), copies inside, best of 3 after a warm-up"
+        out["C1_10M_u32"] = c1
+    except BaseException as e:  # noqa: BLE001
+        note_error("other_configs/C1_10M_u32", e)
+        out["C1_10M_u32"] = {"error": f"{type(e).__name__}: {e}"[:200], "verified": False}
+        if isinstance(e, (SystemExit, AssertionError)):
+            failed.append("C1_10M_u32")
     # C3: 1 B keys of the transform kinds (radix_digits.rs:55-124)
     n3 = 1_000_000_000
-    out["C3_1B_f32_test_shaped"] = run_case("f32", n3, D.FLOAT_TEST, 0.0, 0xB2000003, "C3 f32 test-shaped")
-    out["C3_1B_f32_raw_bits"] = run_case("f32", n3, D.UNIFORM, 0.0, 0xB2000003, "C3 f32 raw")
-    out["C3_1B_f64_raw_bits"] = run_case("f64", n3, D.UNIFORM, 0.0, 0xB2000003, "C3 f64 raw")
-    out["C3_1B_i32"] = run_case("i32", n3, D.UNIFORM, 0.0, 0xB2000003, "C3 i32")
-    out["C3_1B_i64"] = run_case("i64", n3, D.UNIFORM, 0.0, 0xB2000003, "C3 i64")
+    case("C3_1B_f32_test_shaped", "f32", n3, D.FLOAT_TEST, 0.0, 0xB2000003, "C3 f32 test-shaped")
+    case("C3_1B_f32_raw_bits", "f32", n3, D.UNIFORM, 0.0, 0xB2000003, "C3 f32 raw")
+    case("C3_1B_f64_raw_bits", "f64", n3, D.UNIFORM, 0.0, 0xB2000003, "C3 f64 raw")
+    case("C3_1B_i32", "i32", n3, D.UNIFORM, 0.0, 0xB2000003, "C3 i32")
+    case("C3_1B_i64", "i64", n3, D.UNIFORM, 0.0, 0xB2000003, "C3 i64")
     # C4: 2 B u32, skewed / few-unique / presorted (distr.rs families; presorted is the builder's)
     n4 = 2_000_000_000
-    out["C4_2B_u32_zipf_1.0"] = run_case("u32", n4, D.ZIPF, 1.0, 0xB2000004, "C4 zipf")
-    out["C4_2B_u32_step_16"] = run_case("u32", n4, D.STEP, 16, 0xB2000004, "C4 step 16")
-    out["C4_2B_u32_ascending"] = run_case("u32", n4, D.ASCENDING, 0.0, 0xB2000004, "C4 ascending")
-    out["C4_2B_u32_geometric_2^-10"] = run_case("u32", n4, D.GEOMETRIC, 2.0 ** -10, 0xB2000004, "C4 geometric")
+    case("C4_2B_u32_zipf_1.0", "u32", n4, D.ZIPF, 1.0, 0xB2000004, "C4 zipf")
+    case("C4_2B_u32_step_16", "u32", n4, D.STEP, 16, 0xB2000004, "C4 step 16")
+    case("C4_2B_u32_ascending", "u32", n4, D.ASCENDING, 0.0, 0xB2000004, "C4 ascending")
+    case("C4_2B_u32_geometric_2^-10", "u32", n4, D.GEOMETRIC, 2.0 ** -10, 0xB2000004, "C4 geometric")
     # the demo's record shapes (main.rs:104-125): (u32,u32) and (u64,u64) pairs, payload 0 (distr.rs:42-52), 4.0 GB
     for name, kind, pairs in (("records_4GB_u32_u32", "u32", 500_000_000), ("records_4GB_u64_u64", "u64", 250_000_000)):
-        K = rs.Kind[kind.upper()]
-        kb = rs.key_bytes(K)
-        dt = getattr(torch, distr._TORCH_DTYPE[K])
-        pristine = buf_a[: pairs * 2 * kb].view(dt).view(pairs, 2)
-        recs = buf_b[: pairs * 2 * kb].view(dt).view(pairs, 2)
-        col = buf_b[4_000_000_000: 4_000_000_000 + pairs * kb].view(dt)
-        distr.generate(col, K, D.UNIFORM, 0.0, seed=0xB2000005)
-        pristine.zero_()
-        pristine[:, 0] = col
-        total = 0.0
-        for i in range(1 + steps):
-            recs.copy_(pristine)
-            torch.cuda.synchronize()
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a0.record()
-            rs.radix_sort_records(recs, K, 0, workspace=ws)
-            a1.record()
-            torch.cuda.synchronize()
-            if i >= 1:
-                total += a0.elapsed_time(a1)
-        ms = total / steps
-        keycol = recs[:, 0].contiguous()
-        if verify.count_unsorted(keycol, K) != 0 or verify.fingerprint(keycol, K) != verify.fingerprint(col, K):
-            raise SystemExit(f"{name}: record sort failed verification")
-        out[name] = {"records": pairs, "record_bytes": 2 * kb, "ms": round(ms, 4), "grecords_s": round(pairs / ms / 1e6, 3),
-                     "GBps": round(pairs * 2 * kb * (1 + 2 * kb) / ms / 1e6, 1),
-                     "reference_shape": "main.rs:104-125 (KeyUniform pairs, payload 0), largest size", "verified": "keys sorted + key multiset"}
+        try:
+            K = rs.Kind[kind.upper()]
+            kb = rs.key_bytes(K)
+            dt = getattr(torch, distr._TORCH_DTYPE[K])
+            pristine = buf_a[: pairs * 2 * kb].view(dt).view(pairs, 2)
+            recs = buf_b[: pairs * 2 * kb].view(dt).view(pairs, 2)
+            col = buf_b[4_000_000_000: 4_000_000_000 + pairs * kb].view(dt)
+            distr.generate(col, K, D.UNIFORM, 0.0, seed=0xB2000005)
+            pristine.zero_()
+            pristine[:, 0] = col
+            total = 0.0
+            for i in range(1 + steps):
+                recs.copy_(pristine)
+                torch.cuda.synchronize()
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a0.record()
+                rs.radix_sort_records(recs, K, 0, workspace=ws)
+                a1.record()
+                torch.cuda.synchronize()
+                if i >= 1:
+                    total += a0.elapsed_time(a1)
+            ms = total / steps
+            keycol = recs[:, 0].contiguous()
+            if verify.count_unsorted(keycol, K) != 0 or verify.fingerprint(keycol, K) != verify.fingerprint(col, K):
+                raise SystemExit(f"{name}: record sort failed verification")
+            out[name] = {"records": pairs, "record_bytes": 2 * kb, "ms": round(ms, 4), "grecords_s": round(pairs / ms / 1e6, 3),
+                         "GBps": round(pairs * 2 * kb * (1 + 2 * kb) / ms / 1e6, 1),
+                         "reference_shape": "main.rs:104-125 (KeyUniform pairs, payload 0), largest size", "verified": "keys sorted + key multiset"}
+        except BaseException as e:  # noqa: BLE001
+            note_error(f"other_configs/{name}", e)
+            out[name] = {"error": f"{type(e).__name__}: {e}"[:200], "verified": False}
+            if isinstance(e, (SystemExit, AssertionError)):
+                failed.append(name)
     if with_cpu:
-        cores, g = cpu_records_baseline(62_500_000)
-        out["records_cpu_baseline"] = {"grecords_s": round(g, 4), "cores": cores, "kind": "port",
-                                       "sample": "62.5 M (u32,u32) pairs = the demo's 0.5 GB case (main.rs:104), oracle_sort_mt on pair_u32, one run"}
+        try:
+            cores, g = cpu_records_baseline(62_500_000)
+            out["records_cpu_baseline"] = {"grecords_s": round(g, 4), "cores": cores, "kind": "port",
+                                           "sample": "62.5 M (u32,u32) pairs = the demo's 0.5 GB case (main.rs:104), oracle_sort_mt on pair_u32, one run"}
+        except BaseException as e:  # noqa: BLE001
+            note_error("other_configs/records_cpu_baseline", e)
     return out
 
 
@@ -360,6 +385,18 @@ def run_gpu(args):
         if host_group is not None:
             dist.barrier(group=host_group)
 
+    # Nothing after the timed steps may cost the record: every auxiliary leg (parity pre-step, configs[4], alloc-inside,
+    # u32, the other configurations, e2e, cpu_baseline) runs guarded, its failure lands in the line's "errors" list with
+    # the traceback on stderr, the ONE JSON line is printed all the same, and the exit code is non-zero afterwards when a
+    # parity / verification leg was among the failures.
+    errors, failed = [], []
+
+    def note_error(leg, e):
+        import traceback
+        sys.stderr.write(f"[bench.py rank {rank}] leg '{leg}' failed:\n{''.join(traceback.format_exception(type(e), e, e.__traceback__))}\n")
+        sys.stderr.flush()
+        errors.append({"leg": leg, "rank": rank, "msg": f"{type(e).__name__}: {e}"[:300]})
+
     K = rs.Kind.U64
     n = args.n
     c5 = world >= 8 and not args.no_extra and n == N_KEYS  # configs[4] itself, as an extra labelled point
@@ -369,12 +406,25 @@ def run_gpu(args):
     mgpu_parity = None
     if world > 1 and not args.no_parity:
         from tests import _mgpu_worker
-        _mgpu_worker.run_cases(dist, dev, rank, world)            # rank-per-process: fused exchange, overlap, NCCL fallback
+        perr = 0
+        try:
+            _mgpu_worker.run_cases(dist, dev, rank, world)        # rank-per-process: fused exchange, overlap, NCCL fallback
+        except BaseException as e:  # noqa: BLE001  (recorded; the line is still printed and the exit code says so)
+            perr = 1
+            note_error("mgpu_parity/run_cases", e)
         host_barrier()
         if rank == 0:
-            _mgpu_worker.communicator_case(list(range(world)))    # one process over all GPUs (b200sort_mgpu_*)
+            try:
+                _mgpu_worker.communicator_case(list(range(world)))  # one process over all GPUs (b200sort_mgpu_*)
+            except BaseException as e:  # noqa: BLE001
+                perr = 1
+                note_error("mgpu_parity/communicator", e)
         host_barrier()
-        mgpu_parity = "ok"
+        pf = torch.tensor([perr], dtype=torch.int32, device=dev)
+        dist.all_reduce(pf, op=dist.ReduceOp.MAX)
+        mgpu_parity = "ok" if int(pf.item()) == 0 else "FAILED"
+        if mgpu_parity != "ok":
+            failed.append("mgpu_parity")
 
     pristine = distr.empty_keys(n, K, dev)
     distr.generate(pristine, K, distr.Distr.UNIFORM, 0, seed=SEED, index_base=rank * n)
@@ -461,6 +511,11 @@ def run_gpu(args):
                 if last is not None and int(e[0]) < last:
                     ok = False
                 last = int(e[1])
+        if world > 1:  # one verdict for all ranks, so that nobody is left waiting in the next collective
+            okt = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+            if ok and int(okt.item()) == 0:
+                raise SystemExit(f"rank {rank}: {what}: another rank's part of the result failed verification")
         if not ok:
             raise SystemExit(f"rank {rank}: {what}: sort result failed verification (unsorted pairs: {unsorted})")
 
@@ -512,7 +567,7 @@ def run_gpu(args):
     peak, peak_src = peaks()
     achieved = 2.0 * rf_n * KEY_BYTES / (avg_pass * 1e-3) / 1e9
     traffic = None
-    for name in ("r02_traffic.json", "r01_traffic.json"):
+    for name in ("r03_traffic.json", "r02_traffic.json", "r01_traffic.json"):
         try:
             with open(os.path.join(ROOT, "profiles", name)) as fh:
                 tj = json.load(fh)
@@ -525,32 +580,38 @@ def run_gpu(args):
     # ---- configs[4] as stated (16 B u64 keys over 8 GPUs = 2 B per GPU), an extra labelled point at N >= 8
     c5_line = None
     if c5:
-        del pristine, keys, out
-        torch.cuda.empty_cache()
-        n5 = C5_KEYS_PER_GPU
-        k5 = distr.empty_keys(n5, K, dev)
-        t5 = 0.0
-        c5_steps = 2
-        for i in range(1 + c5_steps):
-            distr.generate(k5, K, distr.Distr.UNIFORM, 0, seed=SEED + 5, index_base=rank * n5)  # untimed: fresh unsorted input
-            if i == 0:
-                fp5 = verify.fingerprint(k5, K)
-            barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            o5 = sharded(k5).keys
-            e1.record()
-            torch.cuda.synchronize()
-            if i >= 1:
-                t5 += e0.elapsed_time(e1)
-        verify_result(o5, fp5, "configs[4]")
-        tt5 = torch.tensor([t5], dtype=torch.float64, device=dev)
-        dist.all_reduce(tt5, op=dist.ReduceOp.MAX)
-        ms5 = float(tt5.item()) / c5_steps
-        c5_line = {"workload": f"BASELINE.json configs[4]: {world * n5} uniform u64 keys sharded over {world} B200 ({n5} per GPU)",
-                   "keys_per_gpu": n5, "ms_per_step": round(ms5, 3), "value": round(world * n5 / ms5 / 1e6, 3), "unit": "Gkeys/s",
-                   "steps": c5_steps, "verified": "sorted + multiset fingerprint over all ranks + ascending shard boundaries"}
-        del k5, o5
+        try:
+            del pristine, keys, out
+            torch.cuda.empty_cache()
+            n5 = C5_KEYS_PER_GPU
+            k5 = distr.empty_keys(n5, K, dev)
+            t5 = 0.0
+            c5_steps = 2
+            for i in range(1 + c5_steps):
+                distr.generate(k5, K, distr.Distr.UNIFORM, 0, seed=SEED + 5, index_base=rank * n5)  # untimed: fresh unsorted input
+                if i == 0:
+                    fp5 = verify.fingerprint(k5, K)
+                barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                o5 = sharded(k5).keys
+                e1.record()
+                torch.cuda.synchronize()
+                if i >= 1:
+                    t5 += e0.elapsed_time(e1)
+            verify_result(o5, fp5, "configs[4]")
+            tt5 = torch.tensor([t5], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt5, op=dist.ReduceOp.MAX)
+            ms5 = float(tt5.item()) / c5_steps
+            c5_line = {"workload": f"BASELINE.json configs[4]: {world * n5} uniform u64 keys sharded over {world} B200 ({n5} per GPU)",
+                       "keys_per_gpu": n5, "ms_per_step": round(ms5, 3), "value": round(world * n5 / ms5 / 1e6, 3), "unit": "Gkeys/s",
+                       "steps": c5_steps, "verified": "sorted + multiset fingerprint over all ranks + ascending shard boundaries"}
+            del k5, o5
+        except BaseException as e:  # noqa: BLE001
+            note_error("configs[4]", e)
+            if isinstance(e, (SystemExit, AssertionError)):
+                failed.append("configs[4]")
+        k5 = o5 = None
         torch.cuda.empty_cache()
         pristine = distr.empty_keys(n, K, dev)
         distr.generate(pristine, K, distr.Distr.UNIFORM, 0, seed=SEED, index_base=rank * n)
@@ -561,126 +622,151 @@ def run_gpu(args):
     alloc_inside = None
     if world == 1 and not args.no_u32:
         ws_bytes = int(ws.numel())
-        del ws
-        torch.cuda.empty_cache()
-        ta = []
-        for _ in range(3):
-            keys.copy_(pristine)
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            w = torch.empty(rs.temp_bytes(n, K), dtype=torch.uint8, device=dev)  # cache is empty: a real cudaMalloc
-            rs.radix_sort(keys, K, workspace=w)
-            torch.cuda.synchronize()
-            del w
-            torch.cuda.empty_cache()  # cudaFree
-            ta.append(time.perf_counter() - t0)
-        alloc_inside = {"value": round(n / min(ta) / 1e9, 3), "unit": "Gkeys/s", "ms_per_step": round(min(ta) * 1e3, 3),
-                        "note": "device-resident keys; cudaMalloc + cudaFree of the workspace inside the timed region, host wall clock, best of 3"}
-        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        try:
+            ws = None
+            torch.cuda.empty_cache()
+            ta = []
+            for _ in range(3):
+                keys.copy_(pristine)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                w = torch.empty(rs.temp_bytes(n, K), dtype=torch.uint8, device=dev)  # cache is empty: a real cudaMalloc
+                rs.radix_sort(keys, K, workspace=w)
+                torch.cuda.synchronize()
+                del w
+                torch.cuda.empty_cache()  # cudaFree
+                ta.append(time.perf_counter() - t0)
+            alloc_inside = {"value": round(n / min(ta) / 1e9, 3), "unit": "Gkeys/s", "ms_per_step": round(min(ta) * 1e3, 3),
+                            "note": "device-resident keys; cudaMalloc + cudaFree of the workspace inside the timed region, host wall clock, best of 3"}
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        except BaseException as e:  # noqa: BLE001
+            note_error("alloc_inside", e)
+        if ws is None:
+            torch.cuda.empty_cache()
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
 
     # ---- the metric names u32 too: the same workload shape with 4-byte keys (N = 1 only), reported beside the headline
     u32_line = None
     if world == 1 and not args.no_u32:
-        K4 = rs.Kind.U32
-        p4 = distr.empty_keys(n, K4, dev)
-        distr.generate(p4, K4, distr.Distr.UNIFORM, 0, seed=SEED)
-        k4 = torch.empty_like(p4)
-        fp4 = verify.fingerprint(p4, K4)
-        ms4 = timed_sorts(rs, torch, k4, p4, K4, ws, args.steps, warm=2)
-        if verify.count_unsorted(k4, K4) != 0 or verify.fingerprint(k4, K4) != fp4:
-            raise SystemExit("u32 sort failed verification")
-        k4.copy_(p4)
-        tt4 = rs.sort_timed(k4, K4, workspace=ws, flags=rs.FLAG_NO_SKIP)
-        ap4 = sum(tt4["pass_ms"]) / len(tt4["pass_ms"])
-        u32_line = {"value": round(n / (ms4 * 1e-3) / 1e9, 3), "unit": "Gkeys/s", "ms_per_step": round(ms4, 4),
-                    "workload": f"uniform random u32 keys, {n} elements, single B200", "pass_GBps": round(2.0 * n * 4 / (ap4 * 1e-3) / 1e9, 1),
-                    "pass_frac": round(2.0 * n * 4 / (ap4 * 1e-3) / 1e9 / peak, 4), "avg_launch_ms": round(ap4, 4),
-                    "whole_sort_GBps": round(36.0 * n / (ms4 * 1e-3) / 1e9, 1)}
-        del p4, k4
+        try:
+            K4 = rs.Kind.U32
+            p4 = distr.empty_keys(n, K4, dev)
+            distr.generate(p4, K4, distr.Distr.UNIFORM, 0, seed=SEED)
+            k4 = torch.empty_like(p4)
+            fp4 = verify.fingerprint(p4, K4)
+            ms4 = timed_sorts(rs, torch, k4, p4, K4, ws, args.steps, warm=2)
+            if verify.count_unsorted(k4, K4) != 0 or verify.fingerprint(k4, K4) != fp4:
+                raise SystemExit("u32 sort failed verification")
+            k4.copy_(p4)
+            tt4 = rs.sort_timed(k4, K4, workspace=ws, flags=rs.FLAG_NO_SKIP)
+            ap4 = sum(tt4["pass_ms"]) / len(tt4["pass_ms"])
+            u32_line = {"value": round(n / (ms4 * 1e-3) / 1e9, 3), "unit": "Gkeys/s", "ms_per_step": round(ms4, 4),
+                        "workload": f"uniform random u32 keys, {n} elements, single B200", "pass_GBps": round(2.0 * n * 4 / (ap4 * 1e-3) / 1e9, 1),
+                        "pass_frac": round(2.0 * n * 4 / (ap4 * 1e-3) / 1e9 / peak, 4), "avg_launch_ms": round(ap4, 4),
+                        "whole_sort_GBps": round(36.0 * n / (ms4 * 1e-3) / 1e9, 1)}
+            del p4, k4
+        except BaseException as e:  # noqa: BLE001
+            note_error("u32", e)
+            if isinstance(e, (SystemExit, AssertionError)):
+                failed.append("u32")
 
     # ---- the other configurations of BASELINE.json, at their stated sizes (N = 1)
     others = None
     if world == 1 and not args.no_extra and n == N_KEYS:
-        buf_a = pristine.view(torch.uint8)
-        buf_b = keys.view(torch.uint8)
-        others = other_configs(rs, torch, np, distr, verify, _ffi, dev, buf_a, buf_b, ws, peak, args.steps, not args.no_cpu)
-        distr.generate(pristine, K, distr.Distr.UNIFORM, 0, seed=SEED, index_base=rank * n)  # the buffers were reused
+        try:
+            buf_a = pristine.view(torch.uint8)
+            buf_b = keys.view(torch.uint8)
+            others = other_configs(rs, torch, np, distr, verify, _ffi, dev, buf_a, buf_b, ws, peak, args.steps, not args.no_cpu, note_error, failed)
+            distr.generate(pristine, K, distr.Distr.UNIFORM, 0, seed=SEED, index_base=rank * n)  # the buffers were reused
+        except BaseException as e:  # noqa: BLE001
+            note_error("other_configs", e)
 
     # ---- e2e: ONE pinned host slice through the drop-in C-ABI call, copies inside the timed region
     e2e_steps = 0 if args.no_e2e else max(1, min(args.steps, 5))
     e2e_value, e2e_note, h2d, d2h = None, None, n * KEY_BYTES, n * KEY_BYTES
     e2e_pageable = None
     if e2e_steps and world == 1:
-        host = torch.empty(n, dtype=torch.uint64, pin_memory=True)
-        e2e_total = 0.0
-        for i in range(e2e_steps + 1):
-            host.copy_(pristine)  # untimed: a fresh unsorted HOST input
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            _ffi.check(_ffi.lib().b200sort_keys_host(host.data_ptr(), n, int(K)))
-            dt = time.perf_counter() - t0
-            if i > 0:  # first one is the warm-up (device pool allocation)
-                e2e_total += dt
-        e2e_value = n / (e2e_total / e2e_steps) / 1e9
-        e2e_note = "b200sort_keys_host on one pinned host slice"
-        assert bool((host[1:].view(torch.int64) ^ (-2**63) >= host[:-1].view(torch.int64) ^ (-2**63)).all()), "e2e result not sorted"
-        del host
-        # the same call on PAGEABLE host memory (what a Rust Vec<T> is): the library stages it through
-        # its own pinned bounce buffers with copy threads.  Reported beside the contract's pinned number.
-        pristine_host = pristine.cpu().numpy()
-        pageable = np.empty(n, dtype=np.uint64)
-        tp = 0.0
-        for i in range(3):  # the first one is the warm-up (bounce buffers, copy threads)
-            pageable[...] = pristine_host
-            t0 = time.perf_counter()
-            _ffi.check(_ffi.lib().b200sort_keys_host(pageable.ctypes.data, n, int(K)))
-            if i > 0:
-                tp += time.perf_counter() - t0
-        assert bool(np.all(pageable[1:] >= pageable[:-1])), "pageable e2e result not sorted"
-        e2e_pageable = {"value": round(n / (tp / 2) / 1e9, 3), "unit": "Gkeys/s",
-                        "note": "b200sort_keys_host on an unpinned numpy array (a Rust Vec is pageable too): staged through the "
-                                "library's pinned bounce buffers by its copy threads"}
-        del pageable, pristine_host
+        try:
+            host = torch.empty(n, dtype=torch.uint64, pin_memory=True)
+            e2e_total = 0.0
+            for i in range(e2e_steps + 1):
+                host.copy_(pristine)  # untimed: a fresh unsorted HOST input
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                _ffi.check(_ffi.lib().b200sort_keys_host(host.data_ptr(), n, int(K)))
+                dt = time.perf_counter() - t0
+                if i > 0:  # first one is the warm-up (device pool allocation)
+                    e2e_total += dt
+            e2e_value = n / (e2e_total / e2e_steps) / 1e9
+            e2e_note = "b200sort_keys_host on one pinned host slice"
+            assert bool((host[1:].view(torch.int64) ^ (-2**63) >= host[:-1].view(torch.int64) ^ (-2**63)).all()), "e2e result not sorted"
+            del host
+            # the same call on PAGEABLE host memory (what a Rust Vec<T> is): the library stages it through
+            # its own pinned bounce buffers with copy threads.  Reported beside the contract's pinned number.
+            pristine_host = pristine.cpu().numpy()
+            pageable = np.empty(n, dtype=np.uint64)
+            tp = 0.0
+            for i in range(3):  # the first one is the warm-up (bounce buffers, copy threads)
+                pageable[...] = pristine_host
+                t0 = time.perf_counter()
+                _ffi.check(_ffi.lib().b200sort_keys_host(pageable.ctypes.data, n, int(K)))
+                if i > 0:
+                    tp += time.perf_counter() - t0
+            assert bool(np.all(pageable[1:] >= pageable[:-1])), "pageable e2e result not sorted"
+            e2e_pageable = {"value": round(n / (tp / 2) / 1e9, 3), "unit": "Gkeys/s",
+                            "note": "b200sort_keys_host on an unpinned numpy array (a Rust Vec is pageable too): staged through the "
+                                    "library's pinned bounce buffers by its copy threads"}
+            del pageable, pristine_host
+        except BaseException as e:  # noqa: BLE001
+            note_error("e2e (b200sort_keys_host)", e)
+            if isinstance(e, (SystemExit, AssertionError)):
+                failed.append("e2e (b200sort_keys_host)")
     elif e2e_steps:
         # N > 1: the reference's caller is ONE process with ONE slice: rank 0 calls b200sort_mgpu_keys_host over
         # all N GPUs on a pinned slice of N x n keys; the other ranks free their buffers and wait on the host
-        del keys, ws, exchange, sendbuf, ws2
+        keys = ws = exchange = sendbuf = ws2 = None  # free this rank's buffers: rank 0 drives every GPU now
         out = None
         torch.cuda.empty_cache()
         host_barrier()
         res = [0.0, 0.0]
         if rank == 0:
-            total_keys = world * n
             try:
-                host = torch.empty(total_keys, dtype=torch.uint64, pin_memory=True)
-            except Exception:  # noqa: BLE001  (the box cannot pin N x 8 GB: one GPU's share, and the line says so)
-                total_keys = n
-                host = torch.empty(total_keys, dtype=torch.uint64, pin_memory=True)
-            comm = mgpu.Communicator(list(range(world)))
-            tot = 0.0
-            for i in range(e2e_steps + 1):
-                for r in range(total_keys // n):  # untimed: a fresh unsorted HOST input, the ranks' shards side by side
-                    distr.generate(pristine, K, distr.Distr.UNIFORM, 0, seed=SEED, index_base=r * n)
-                    host[r * n:(r + 1) * n].copy_(pristine)
-                torch.cuda.synchronize()
-                t0 = time.perf_counter()
-                comm.sort_host(host, K)
-                dt = time.perf_counter() - t0
-                if i > 0:
-                    tot += dt
-            hs = host.view(torch.int64) ^ (-2**63)
-            step = 1 << 28
-            for lo in range(0, total_keys - 1, step):
-                hi = min(total_keys, lo + step + 1)
-                assert bool((hs[lo + 1:hi] >= hs[lo:hi - 1]).all()), "e2e result not sorted"
-            comm.close()
-            res = [float(total_keys), tot / e2e_steps]
-            del host
+                total_keys = world * n
+                try:
+                    host = torch.empty(total_keys, dtype=torch.uint64, pin_memory=True)
+                except Exception:  # noqa: BLE001  (the box cannot pin N x 8 GB: one GPU's share, and the line says so)
+                    total_keys = n
+                    host = torch.empty(total_keys, dtype=torch.uint64, pin_memory=True)
+                comm = mgpu.Communicator(list(range(world)))
+                host_np = host.numpy()  # Communicator.sort_host takes a writable numpy array (same pinned memory)
+                tot = 0.0
+                for i in range(e2e_steps + 1):
+                    for r in range(total_keys // n):  # untimed: a fresh unsorted HOST input, the ranks' shards side by side
+                        distr.generate(pristine, K, distr.Distr.UNIFORM, 0, seed=SEED, index_base=r * n)
+                        host[r * n:(r + 1) * n].copy_(pristine)
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    comm.sort_host(host_np, K)
+                    dt = time.perf_counter() - t0
+                    if i > 0:
+                        tot += dt
+                hs = host.view(torch.int64) ^ (-2**63)
+                step = 1 << 28
+                for lo in range(0, total_keys - 1, step):
+                    hi = min(total_keys, lo + step + 1)
+                    assert bool((hs[lo + 1:hi] >= hs[lo:hi - 1]).all()), "e2e result not sorted"
+                comm.close()
+                res = [float(total_keys), tot / e2e_steps]
+                del host_np, host
+            except BaseException as e:  # noqa: BLE001
+                note_error("e2e (b200sort_mgpu_keys_host)", e)
+                if isinstance(e, (SystemExit, AssertionError)):
+                    failed.append("e2e (b200sort_mgpu_keys_host)")
         host_barrier()
         tr = torch.tensor(res, dtype=torch.float64, device=dev)
         dist.broadcast(tr, src=0)
         total_keys, sec = int(tr[0].item()), float(tr[1].item())
-        e2e_value = total_keys / sec / 1e9
+        e2e_value = total_keys / sec / 1e9 if sec > 0 else None  # None: rank 0's leg failed (see "errors")
         h2d = d2h = total_keys * KEY_BYTES
         e2e_note = (f"b200sort_mgpu_keys_host: one process (rank 0), one pinned host slice of {total_keys} keys over all {world} GPUs"
                     + ("" if total_keys == world * n else " (the box could not pin N x 8 GB: one GPU's share of the workload)"))
@@ -689,16 +775,19 @@ def run_gpu(args):
         if dist is not None:
             dist.barrier()
             dist.destroy_process_group()
-        return 0
+        return 1 if failed else 0
 
     cpu = None
     if world == 1 and not args.no_cpu:
-        ncpu = min(n, args.cpu_keys)
-        cores, res = cpu_baseline(ncpu)
-        cpu = {"value": round(res["radix_sort"], 4), "unit": "Gkeys/s", "cores": cores, "kind": "port",
-               "sample": (f"{ncpu} uniform u64 keys ({'the whole workload' if ncpu == n else f'{ncpu / n:.2f} of the workload'}), one run each: "
-                          f"C restatement of RadixSort::radix_sort (mod.rs:61-176) = {res['radix_sort']:.4f} Gkeys/s; of the rayon variant "
-                          f"radix_sort4 (mod.rs:405-466) = {res['radix_sort4']:.4f} Gkeys/s; {cores} host threads")}
+        try:
+            ncpu = min(n, args.cpu_keys)
+            cores, res = cpu_baseline(ncpu)
+            cpu = {"value": round(res["radix_sort"], 4), "unit": "Gkeys/s", "cores": cores, "kind": "port",
+                   "sample": (f"{ncpu} uniform u64 keys ({'the whole workload' if ncpu == n else f'{ncpu / n:.2f} of the workload'}), one run each: "
+                              f"C restatement of RadixSort::radix_sort (mod.rs:61-176) = {res['radix_sort']:.4f} Gkeys/s; of the rayon variant "
+                              f"radix_sort4 (mod.rs:405-466) = {res['radix_sort4']:.4f} Gkeys/s; {cores} host threads")}
+        except BaseException as e:  # noqa: BLE001
+            note_error("cpu_baseline", e)
 
     # NVLink roofline of the exchange (rank 0's phase time): every rank sends (world-1)/world of its keys
     nvlink = None
@@ -743,10 +832,35 @@ def run_gpu(args):
         line["e2e_pageable"] = e2e_pageable
     if cpu is not None:
         line["cpu_baseline"] = cpu
+    line["errors"] = errors
+    # the numbers BASELINE.json's metric names ("sorted Gkeys/s (u32, u64)") and the other configurations, compact and LAST:
+    # whoever keeps only the tail of this line keeps these
+    oc = others or {}
+    g = lambda name, key: (oc.get(name) or {}).get(key)  # noqa: E731
+    summary = {
+        "u64_gkeys_s": round(value, 3), "u64_pass_frac": round(achieved / peak, 4),
+        "u32_gkeys_s": (u32_line or {}).get("value"), "u32_pass_frac": (u32_line or {}).get("pass_frac"),
+        "e2e_gkeys_s": round(e2e_value, 3) if e2e_value is not None else None,
+        "e2e_pageable_gkeys_s": (e2e_pageable or {}).get("value"),
+        "alloc_inside_gkeys_s": (alloc_inside or {}).get("value"),
+        "c1_ms": g("C1_10M_u32", "ms"), "c1_host_call_ms": g("C1_10M_u32", "host_call_ms"),
+        "c3_f32_gkeys_s": g("C3_1B_f32_test_shaped", "gkeys_s"), "c3_f32_raw_gkeys_s": g("C3_1B_f32_raw_bits", "gkeys_s"),
+        "c3_f64_gkeys_s": g("C3_1B_f64_raw_bits", "gkeys_s"), "c3_i32_gkeys_s": g("C3_1B_i32", "gkeys_s"),
+        "c3_i64_gkeys_s": g("C3_1B_i64", "gkeys_s"),
+        "c4_zipf_gkeys_s": g("C4_2B_u32_zipf_1.0", "gkeys_s"), "c4_step16_gkeys_s": g("C4_2B_u32_step_16", "gkeys_s"),
+        "c4_ascending_gkeys_s": g("C4_2B_u32_ascending", "gkeys_s"), "c4_geometric_gkeys_s": g("C4_2B_u32_geometric_2^-10", "gkeys_s"),
+        "records_u32_u32_grecords_s": g("records_4GB_u32_u32", "grecords_s"), "records_u64_u64_grecords_s": g("records_4GB_u64_u64", "grecords_s"),
+        "c5_16B_keys_gkeys_s": (c5_line or {}).get("value"), "mgpu_parity": mgpu_parity,
+        "cpu_gkeys_s": (cpu or {}).get("value"), "n_errors": len(errors), "failed": failed,
+    }
+    line["summary"] = {k_: v_ for k_, v_ in summary.items() if v_ is not None or k_ in ("mgpu_parity",)}
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+    if failed:
+        sys.stderr.write(f"bench.py: parity / verification failed in: {failed}\n")
+        return 1
     return 0
 
 
