@@ -101,6 +101,10 @@ template <class K, class V>
 inline void radix_sort(std::pair<K, V>* data, std::size_t len) {
     using R = std::pair<K, V>;
     static_assert(std::is_trivially_copyable_v<K> && std::is_trivially_copyable_v<V>, "elements are moved bit for bit");
+    // the two record shapes the library sorts (b200sort_api.cu, check_record_shape); anything else fails to compile
+    // here instead of returning B200SORT_ERR_UNSUPPORTED_KIND at run time where the reference would have sorted
+    static_assert((sizeof(R) == 8 && sizeof(K) == 4) || (sizeof(R) == 16 && sizeof(K) == 8),
+                  "libb200sort sorts (K, V) records of 8 bytes with a 4-byte key or of 16 bytes with an 8-byte key only");
     // layout, not assumed: a Rust tuple is repr(Rust) and a std::pair has padding rules of its own
     const R probe{};
     const std::size_t key_off =

@@ -35,9 +35,25 @@ gpu_key!(usize => U32, isize => I32);
 
 // radix_digits.rs:126-136: the digit of a tuple is the digit of `.0`; `.1` rides along.
 // Tuples are repr(Rust): the offset of `.0` is computed, never assumed.
-impl<T: GpuKey, U: Send + Sync> GpuKey for (T, U) {
+// Bounds spelled out as in the reference's own tuple impl (radix_digits.rs:126-130: `T: RadixDigits + Send + Sync`,
+// `U: Send + Sync`), which is what the supertrait `RadixDigits` of `GpuKey` requires of `(T, U)`.  (`RadixDigits:
+// Send + Sync` at radix_digits.rs:1 already implies them for T; repeating them keeps the two impls side by side.)
+// The library sorts two record shapes (b200sort_api.cu, check_record_shape): a 4-byte key in an 8-byte
+// record and an 8-byte key in a 16-byte record.  Any other `(T, U)` is refused HERE, when the constant is
+// evaluated for the concrete types (a compile error at the call site), instead of a panic at run time
+// where the reference would have sorted.
+impl<T: GpuKey + Send + Sync, U: Send + Sync> GpuKey for (T, U) {
     const KIND: Kind = T::KIND;
-    const KEY_OFFSET: usize = std::mem::offset_of!((T, U), 0) + T::KEY_OFFSET;
+    const KEY_OFFSET: usize = {
+        let rec = std::mem::size_of::<(T, U)>();
+        let key = std::mem::size_of::<T>();
+        assert!(
+            (rec == 8 && key == 4) || (rec == 16 && key == 8),
+            "libb200sort sorts (K, V) records of 8 bytes with a 4-byte key or of 16 bytes with an 8-byte key only"
+        );
+        assert!(!T::IS_RECORD, "nested tuples are not a record shape of the library");
+        std::mem::offset_of!((T, U), 0) + T::KEY_OFFSET
+    };
     const IS_RECORD: bool = true;
 }
 

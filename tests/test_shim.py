@@ -99,3 +99,19 @@ def test_patch_applies_to_the_reference(tmp_path):
     # untouched: the reference's tests and call sites
     for f in ("src/radix_sort/tests.rs", "src/main.rs", "src/radix_sort/radix_digits.rs", "src/distr.rs"):
         assert (crate / f).read_bytes() == open(os.path.join(ref, f), "rb").read()
+
+
+def test_tuple_impl_is_bounded_like_the_reference_and_by_the_library_shapes():
+    """radix_digits.rs:126-130 implements RadixDigits for (T, U) where T: RadixDigits + Send + Sync; GpuKey has
+    RadixDigits as a supertrait, so its tuple impl needs the same bounds.  And the shapes it admits are exactly
+    those check_record_shape (b200sort_api.cu) admits: refused at compile time, not by a panic at run time."""
+    gpu = open(os.path.join(ROOT, "shim", "src", "radix_sort", "gpu.rs")).read()
+    assert re.search(r"impl<T:\s*GpuKey\s*\+\s*Send\s*\+\s*Sync,\s*U:\s*Send\s*\+\s*Sync>\s*GpuKey\s+for\s+\(T,\s*U\)", gpu)
+    ref = open("/root/reference/src/radix_sort/radix_digits.rs").read() if os.path.exists("/root/reference") else None
+    if ref is not None:
+        assert re.search(r"impl<T, U> RadixDigits for \(T, U\)\s*where\s*T:\s*RadixDigits\s*\+\s*Send\s*\+\s*Sync,\s*U:\s*Send\s*\+\s*Sync,", ref)
+    api = open(os.path.join(ROOT, "radix_sort_b200", "csrc", "b200sort_api.cu")).read()
+    assert "rec_bytes == 8 && kb == 4" in api and "rec_bytes == 16 && kb == 8" in api
+    assert "(rec == 8 && key == 4) || (rec == 16 && key == 8)" in gpu
+    hpp = open(os.path.join(ROOT, "include", "radix_sort.hpp")).read()
+    assert "(sizeof(R) == 8 && sizeof(K) == 4) || (sizeof(R) == 16 && sizeof(K) == 8)" in hpp
