@@ -268,10 +268,7 @@ int sort_front(const SortCall& c) {
             a.ticket = tickets + (size_t)p * L.portions + q;
             a.stats = stats;
             a.force_rerank = force_rerank() ? 1u : 0u;
-            static const unsigned stagger = [] { const char* e = std::getenv("B200SORT_STAGGER_NS"); return e ? (unsigned)std::atoi(e) : 0u; }();
             a.opaque_zero = 0u;
-            a.stagger_ns = stagger;
-            a.first_wave = 2u * 148u;
             a.prm = prm;
             lb_cursor += a.num_tiles;
             B200_CU((launch_pass_idx<FAM, W>(variant, a, st)));

@@ -82,16 +82,17 @@ template <> struct Variants<FAM_KEYS, 16> { static constexpr VariantDesc v[] = {
 template <> struct Variants<FAM_RECORDS, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0x2000}, {3, 512, 12, 2, 0}}; };
 #define B200_NV_RECORDS_16 2
 template <> struct Variants<FAM_RECORDS, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0x2000}, {3, 256, 12, 2, 0}}; };
+// (the partition is a single, non-stable pass 0: its write-out never verifies, so FEAT_STG would be masked out anyway)
 #define B200_NV_PARTITION_1 1
-template <> struct Variants<FAM_PARTITION, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0x2000}}; };
+template <> struct Variants<FAM_PARTITION, 1> { static constexpr VariantDesc v[] = {{0, 512, 32, 2, 0}}; };
 #define B200_NV_PARTITION_2 1
-template <> struct Variants<FAM_PARTITION, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0x2000}}; };
+template <> struct Variants<FAM_PARTITION, 2> { static constexpr VariantDesc v[] = {{0, 512, 24, 2, 0}}; };
 #define B200_NV_PARTITION_4 1
-template <> struct Variants<FAM_PARTITION, 4> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0x2000}}; };
+template <> struct Variants<FAM_PARTITION, 4> { static constexpr VariantDesc v[] = {{0, 512, 16, 2, 0}}; };
 #define B200_NV_PARTITION_8 1
-template <> struct Variants<FAM_PARTITION, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0x2000}}; };
+template <> struct Variants<FAM_PARTITION, 8> { static constexpr VariantDesc v[] = {{0, 512, 12, 2, 0}}; };
 #define B200_NV_PARTITION_16 1
-template <> struct Variants<FAM_PARTITION, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0x2000}}; };
+template <> struct Variants<FAM_PARTITION, 16> { static constexpr VariantDesc v[] = {{0, 256, 12, 2, 0}}; };
 
 template <int FAM, int W> constexpr int num_variants() { return (int)(sizeof(Variants<FAM, W>::v) / sizeof(VariantDesc)); }
 

@@ -67,7 +67,10 @@ __device__ __forceinline__ u128 ld_elem<u128>(const u128* p) {
 // the generic window check.  Peer-mapped receive buffers (K7) are global addresses too.
 // No "memory" clobber: the write-out keeps its shared-memory loads of the next rows in flight
 // across these stores (with the clobber pass 0 of a u64 sort was 4 % slower); every reader of
-// the stored data is behind a barrier or a kernel boundary.
+// the stored data is behind a barrier or a kernel boundary.  What this relies on: write_out is the LAST
+// user of the destination buffer inside the kernel -- nothing after it loads from or stores to the addresses
+// written here with ordinary C++ accesses, which the compiler would be free to move across these asm stores.
+// (Keep it that way, or give the last store of each thread a "memory" clobber.)
 __device__ __forceinline__ void st_global(unsigned long long addr, unsigned char v) { asm volatile("st.global.u8 [%0], %1;" ::"l"(addr), "r"((unsigned)v)); }
 __device__ __forceinline__ void st_global(unsigned long long addr, unsigned short v) { asm volatile("st.global.u16 [%0], %1;" ::"l"(addr), "h"(v)); }
 __device__ __forceinline__ void st_global(unsigned long long addr, unsigned int v) { asm volatile("st.global.u32 [%0], %1;" ::"l"(addr), "r"(v)); }
@@ -289,8 +292,6 @@ struct PassArgs {
     uint32_t* stats;                     // [0] tiles that took the re-rank fallback
     uint32_t force_rerank;               // test hook: every tile takes the re-rank fallback (b200sort_debug_force_rerank)
     uint32_t opaque_zero;                // always 0, but ptxas cannot know: see pass_s in rank_and_scatter
-    uint32_t stagger_ns;                 // experiment (B200SORT_STAGGER_NS): the second CTA to arrive on an SM in the first
-    uint32_t first_wave;                 //   wave (tickets < first_wave) waits this long, so that the two CTAs of an SM run out of phase
     typename Tr::Params prm;
 };
 
@@ -837,20 +838,6 @@ onesweep_pass_kernel(const __grid_constant__ PassArgs<Tr> a) {
     if (threadIdx.x == 0) ticket = atomicAdd(a.ticket, 1u);
     const PassPlan pp = a.plan->pass[a.pass];
     if (pp.skip) return;
-    if (a.stagger_ns && threadIdx.x == 0 && ticket < a.first_wave && a.pass < 12) {
-        unsigned smid;
-        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-        const unsigned bit = 1u << (smid & 31);
-        if (atomicOr(a.stats + 1 + a.pass * 5 + (smid >> 5), bit) & bit) {
-            unsigned long long t0, t1;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-            do {
-                __nanosleep(200);
-                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-            } while (t1 - t0 < a.stagger_ns);
-        }
-    }
-
     extern __shared__ __align__(128) unsigned char smem_raw[];
     PassShared<Tr, THREADS, ITEMS> sh(smem_raw, SM::TILE_BYTES);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
