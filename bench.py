@@ -450,6 +450,9 @@ def run_gpu(args):
     # (measured slower than the one-piece exchange at N = 2 and N = 8 -- profiles/r01_bench_n*_overlap_*.json -- so opt-in)
     overlap = exchange is not None and args.overlap == "on" and 2 * world <= mgpu.MAX_RANKS
     ws2 = torch.empty(rs.temp_bytes(int(n * 0.75) + 1024, K), dtype=torch.uint8, device=dev) if overlap else None
+    claim = exchange is not None and args.claim == "on" and not overlap
+    if claim:
+        exchange_note += "; count-free: K7 tiles claim room in the receive buffers through cursors on the destination GPUs"
     if overlap:
         exchange_note += "; exchange in two pieces, the second overlapped with the local sort of the first"
 
@@ -460,7 +463,7 @@ def run_gpu(args):
 
     def sharded(k_in, timings=None):
         return mgpu.sort_sharded(k_in, K, workspace=ws, send_buffer=sendbuf, exchange=exchange, overlap=overlap,
-                                 workspace2=ws2, timings=timings)
+                                 workspace2=ws2, timings=timings, claim=claim)
 
     def one_step():
         """returns (elapsed ms on the device, result tensor)"""
@@ -880,6 +883,8 @@ def main():
                     help="skip the host-buffer leg (evidence runs at sizes whose pinned host copies would not fit the box)")
     ap.add_argument("--overlap", default="off", choices=["on", "off"],
                     help="N > 1, fused exchange: send the buckets in two pieces and sort the first while the second travels")
+    ap.add_argument("--claim", default="off", choices=["on", "off"],
+                    help="N > 1, fused exchange: count-free K7 (tiles claim room in the receive buffers through cursors)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "fused", "nccl"],
                     help="N > 1: fused K7 peer stores, NCCL all-to-all, or fused with fallback (default)")
     args = ap.parse_args()

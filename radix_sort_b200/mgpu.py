@@ -31,18 +31,20 @@ Fused form (`sort_sharded(..., exchange=PeerExchange(...))`): steps 3-5 become
 so the keys cross NVLink inside the partition kernel's write-out and are never
 staged in a send buffer or copied by a separate collective.
 
-Claim form (the default whenever the exchange has a control block, round 2): no count
-phase and no count all_gather at all --
-    3*. b200sort_partition_claim_device  one read of the shard; every K7 tile claims
+Claim form (OPT-IN: `sort_sharded(..., exchange=..., claim=True)`; the counting form above
+stays the default): no count phase and no count matrix --
+    3*. every rank zeroes its cursor, barrier
+    4*. b200sort_partition_claim_device  one read of the shard; every K7 tile claims
         room in the destination's receive buffer with ONE system-scope atomicAdd on a
         cursor that lives on the destination GPU, and stores its keys there (the order
         inside a destination is free: it is sorted next)
-    4*. barrier; the cursors now hold every rank's receive count
-and, with `staged=True`, every rank's range is cut in two by one more splitter: the
-FIRST halves travel inside K7 as above, the SECOND halves are claimed into a local
-staging buffer (one region per destination) and cross NVLink afterwards on the copy
-engines (cudaMemcpyAsync on a side stream) WHILE every rank already sorts its first
-half -- the exchange of half of the bytes costs no SM time and no wall time.
+    5*. barrier; the cursors now hold every rank's receive count.  One small all_gather
+        of (cursor, overflow flags) tells every rank the same thing: if any claim passed
+        a receive buffer's capacity nothing of that claim was stored, and ALL ranks take
+        the counting form instead (the cursors still hold the true sizes).
+A staged variant (second halves claimed into a local staging buffer and moved by the copy
+engines under the first local sort) exists in CudaOps.partition_claim(staged=True) and
+PeerExchange(staging=True) but nothing drives it yet: it is not part of sort_sharded.
 
 The device steps go through an `ops` object so that the host-side logic (sample
 positions, splitter choice, count exchange, offsets) runs under gloo on CPU in
@@ -127,7 +129,7 @@ class PeerExchange:
     CTRL_BYTES = 512  # per rank, behind the receive area: [0] cursor of the receive buffer, [1..16] cursors of the
                       # staging regions (one per destination), [32] overflow flags (u32) -- int64 words
 
-    def __init__(self, capacity_keys: int, key_bytes: int, device, group=None, staging: bool = True):
+    def __init__(self, capacity_keys: int, key_bytes: int, device, group=None, staging: bool = False):
         import torch
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
@@ -144,7 +146,8 @@ class PeerExchange:
         self.recv_rows = self.buf[: self.capacity * self.key_bytes].view(self.capacity, self.key_bytes)
         self.ctrl = self.buf[self.recv_bytes:].view(torch.int64)      # this rank's control block
         self.ctrl.zero_()
-        # staging buffer of the second halves: one region per destination rank (plain device memory)
+        # staging buffer of the second halves (opt-in, not used by sort_sharded: world x capacity / world keys of HBM):
+        # one region per destination rank (plain device memory)
         self.stage_cap = self.capacity // max(1, self.world) if staging else 0
         self.stage = (torch.empty(self.world * self.stage_cap * self.key_bytes, dtype=torch.uint8, device=device)
                       if staging and self.stage_cap else None)
@@ -164,6 +167,13 @@ class PeerExchange:
             v = self.handle.get_buffer(rank, (self.capacity * self.key_bytes,), torch.uint8, 0).view(self.capacity, self.key_bytes)
             self._peer_views[rank] = v
         return v
+
+    def reset_cursors(self):
+        """Claim form: zero this rank's cursors and overflow flags on the current stream, then a barrier -- after
+        it every rank's cursors are zero and every rank has reached this point of ITS stream, i.e. has consumed
+        the previous result, so peers may start claiming and storing."""
+        self.ctrl.zero_()
+        self.handle.barrier(channel=0)
 
     def barrier(self, channel: int = 0):
         """Device-side barrier on the current stream: every rank's stores into
@@ -376,7 +386,7 @@ class ShardedResult:
 
 def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 << 14, seed: int = 0xB200,
                  workspace=None, send_buffer=None, exchange=None, timings: Optional[dict] = None,
-                 overlap: bool = False, workspace2=None) -> ShardedResult:
+                 overlap: bool = False, workspace2=None, claim: bool = False) -> ShardedResult:
     """Sort keys sharded over the ranks of `group`.  `keys`: this rank's shard
     (contiguous CUDA tensor; (n, 2) uint64 for 128-bit kinds).  Collective: every
     rank of the group must call it.  Returns this rank's slice of the sorted order
@@ -391,7 +401,12 @@ def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 
     overlap (fused path, world <= 8): every rank's range is cut in two by one more
     splitter; the first halves are exchanged, then the second halves cross NVLink on
     a side stream WHILE every rank already sorts its first half (workspace2: a second
-    sort workspace, the partition state in `workspace` is still in use then)."""
+    sort workspace, the partition state in `workspace` is still in use then).
+
+    claim (fused path, without overlap): the count-free exchange of the module docstring -- K7 tiles claim
+    room in the destinations' receive buffers through cursors instead of counting first.  The result has no
+    per-sender counts then: send_counts is None, recv_counts[d] = keys rank d received.  Falls back to the
+    counting form, on all ranks together, when a receive buffer would overflow."""
     import torch
     import torch.distributed as dist
     k = Kind(kind)
@@ -447,6 +462,25 @@ def sort_sharded(keys, kind, *, group=None, ops=None, samples_per_rank: int = 1 
     fine = np.ascontiguousarray(np.stack(picks))
     splitters = np.ascontiguousarray(fine[1::2]) if halves else fine  # the world - 1 range boundaries
     mark("splitters")
+
+    if exchange is not None and claim and not halves and hasattr(ops, "partition_claim"):
+        ws = ops.workspace_for(n_local, k, workspace)
+        exchange.reset_cursors()
+        ops.partition_claim(rows, k, splitters, ws, exchange, staged=False)
+        exchange.barrier()
+        mine2 = exchange.ctrl[[0, 32]].clone()  # [keys claimed in my receive buffer, buckets I could not store (bits)]
+        both = [torch.zeros_like(mine2) for _ in range(world)]
+        dist.all_gather(both, mine2, group=group)
+        info = np.stack([ops.to_host(b) for b in both])  # world x 2, the same on every rank
+        mark("exchange")
+        if not info[:, 1].any() and int(info[:, 0].max()) <= exchange.capacity:
+            n_out = int(info[rank, 0])
+            recv = exchange.recv_rows[:n_out]
+            ops.local_sort(recv, k, ws)
+            mark("local_sort")
+            finish()
+            return ShardedResult(typed(recv), n_out, None, [int(x) for x in info[:, 0]], splitters)
+        # a receive buffer would overflow: the counting form below decides what to do, identically on every rank
 
     if halves:
         # 3''. count per SUB-range  4''. count matrix -> offsets of my keys in every sub-range

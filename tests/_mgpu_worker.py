@@ -24,17 +24,20 @@ def run_cases(dist, dev, rank, world):
         a = rng.integers(0, 2**64, size=n, dtype=np.uint64)
         if case == "few_unique":
             a = (a % 5) * 1000
-        for use_exchange, overlap in ((True, False), (True, True), (False, False)):
+        # (fused exchange, overlapped in two pieces, count-free claim form); the last is the NCCL all-to-all path
+        for use_exchange, overlap, claim in ((True, False, False), (True, True, False), (True, False, True), (False, False, False)):
             if overlap and 2 * world > mgpu.MAX_RANKS:
                 continue
             keys = torch.from_numpy(a.copy()).to(dev)
-            res = mgpu.sort_sharded(keys, rs.Kind.U64, exchange=exchange if use_exchange else None, overlap=overlap)
+            res = mgpu.sort_sharded(keys, rs.Kind.U64, exchange=exchange if use_exchange else None, overlap=overlap, claim=claim)
+            if claim and case != "overflow":
+                assert res.send_counts is None, "the claim form must have run (it has no per-sender counts)"
             mine = res.keys.cpu().numpy().copy()
             gathered = [None] * world
             dist.all_gather_object(gathered, (a, mine))
             whole_in = np.concatenate([g[0] for g in gathered])
             whole_out = np.concatenate([g[1] for g in gathered])
-            assert np.array_equal(whole_out, np.sort(whole_in)), (case, use_exchange, overlap)
+            assert np.array_equal(whole_out, np.sort(whole_in)), (case, use_exchange, overlap, claim)
             torch.cuda.synchronize()
             dist.barrier()
     del exchange

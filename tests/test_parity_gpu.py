@@ -672,6 +672,102 @@ def test_partition_count_then_exchange_into_separate_buffers(kind, pieces, cuda)
     assert _ref.same_bits(d_in.cpu().numpy(), a)
 
 
+@pytest.mark.parametrize("kind", ["u32", "u64", "f64"])
+def test_partition_claim_two_writers_into_shared_regions(kind, cuda):
+    """The count-free form of K7 (b200sort_partition_claim_device) on one device: two "ranks" (two shards,
+    one launch each) claim room in the SAME four regions through the same four cursors, as two GPUs would in
+    each other's receive buffers.  The order inside a region is free, so regions are compared as multisets
+    (sorted) with what b200sort_partition_device gives for the concatenated input; the cursors must end at
+    the bucket sizes and no overflow bit may be set."""
+    import torch
+    n = 1_200_003
+    a = _ref.random_keys(kind, n, seed=61)
+    srt = _ref.expected_sorted(a, kind)
+    nsplit = 3
+    spl = np.ascontiguousarray(srt[[n * (j + 1) // (nsplit + 1) for j in range(nsplit)]])
+    L = _ffi.lib()
+    k = _kind(kind)
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    d_all = _to_device(a, cuda)
+    # the reference split: the counting partition of the whole input
+    d_ref = torch.empty_like(d_all)
+    ws = torch.empty(rs.temp_bytes(n, k), dtype=torch.uint8, device=cuda)
+    counts = torch.zeros(nsplit + 1, dtype=torch.int64, device=cuda)
+    rc = L.b200sort_partition_device(d_all.data_ptr(), d_ref.data_ptr(), ws.data_ptr(), ws.numel(), n, int(k),
+                                     spl.ctypes.data, nsplit, counts.data_ptr(), st)
+    assert rc == 0, L.b200sort_last_error()
+    cnt = counts.cpu().numpy().tolist()
+    ref = d_ref.cpu().numpy()
+    # two writers: shards of unequal size
+    cut = 700_001
+    shards = [d_all[:cut], d_all[cut:]]
+    cap = [c + 17 for c in cnt]
+    fill = 0xEE
+    regions = [torch.full((cap[r] * a.itemsize,), fill, dtype=torch.uint8, device=cuda).view(d_all.dtype) for r in range(nsplit + 1)]
+    ctrl = torch.zeros(nsplit + 2, dtype=torch.int64, device=cuda)  # cursors 0..nsplit, then the flag word
+    bases = (ctypes.c_void_p * (nsplit + 1))(*[r_.data_ptr() for r_ in regions])
+    cur = (ctypes.c_uint64 * (nsplit + 1))(*[ctrl.data_ptr() + 8 * r for r in range(nsplit + 1)])
+    caps = (ctypes.c_uint64 * (nsplit + 1))(*cap)
+    flags = ctypes.c_void_p(ctrl.data_ptr() + 8 * (nsplit + 1))
+    for sh in shards:
+        rc = L.b200sort_partition_claim_device(sh.data_ptr(), ws.data_ptr(), ws.numel(), int(sh.shape[0]), int(k),
+                                               spl.ctypes.data, nsplit, bases, cur, caps, flags, st)
+        assert rc == 0, L.b200sort_last_error()
+    torch.cuda.synchronize()
+    c = ctrl.cpu().numpy()
+    assert c[: nsplit + 1].tolist() == cnt, "cursors must end at the bucket sizes"
+    assert int(c[nsplit + 1]) == 0, "no region overflowed"
+    pad = np.frombuffer(bytes([fill]) * a.itemsize, dtype=a.dtype)[0]
+    off = 0
+    for r in range(nsplit + 1):
+        got = regions[r].cpu().numpy()
+        want = ref[off: off + cnt[r]]
+        off += cnt[r]
+        assert _ref.same_bits(_ref.expected_sorted(got[: cnt[r]].copy(), kind), _ref.expected_sorted(want.copy(), kind)), f"region {r}"
+        assert _ref.same_bits(got[cnt[r]:], np.full(cap[r] - cnt[r], pad, dtype=a.dtype)), f"region {r}: stores past the claim"
+    assert _ref.same_bits(d_all.cpu().numpy(), a)  # input untouched
+
+
+def test_partition_claim_overflow_sets_the_flag_and_keeps_counting(cuda):
+    """A region that is too small: the tiles whose claim passes the capacity store nothing and set the bucket's
+    bit in the flag word; the cursor still counts every key, so the caller learns the true size and can take
+    the exact (counting) path instead."""
+    import torch
+    kind, n, nsplit = "u64", 900_000, 3
+    a = _ref.random_keys(kind, n, seed=62)
+    srt = _ref.expected_sorted(a, kind)
+    spl = np.ascontiguousarray(srt[[n * (j + 1) // (nsplit + 1) for j in range(nsplit)]])
+    dest = np.searchsorted(spl, a, side="right")
+    cnt = np.bincount(dest, minlength=nsplit + 1).tolist()
+    L = _ffi.lib()
+    k = _kind(kind)
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    d_in = _to_device(a, cuda)
+    ws = torch.empty(rs.temp_bytes(n, k), dtype=torch.uint8, device=cuda)
+    cap = list(cnt)
+    cap[2] = cnt[2] // 2  # bucket 2 does not fit
+    fill = 0xEE
+    regions = [torch.full(((cap[r] + 8) * 8,), fill, dtype=torch.uint8, device=cuda).view(d_in.dtype) for r in range(nsplit + 1)]
+    ctrl = torch.zeros(nsplit + 2, dtype=torch.int64, device=cuda)
+    bases = (ctypes.c_void_p * (nsplit + 1))(*[r_.data_ptr() for r_ in regions])
+    cur = (ctypes.c_uint64 * (nsplit + 1))(*[ctrl.data_ptr() + 8 * r for r in range(nsplit + 1)])
+    caps = (ctypes.c_uint64 * (nsplit + 1))(*cap)
+    flags = ctypes.c_void_p(ctrl.data_ptr() + 8 * (nsplit + 1))
+    rc = L.b200sort_partition_claim_device(d_in.data_ptr(), ws.data_ptr(), ws.numel(), n, int(k), spl.ctypes.data, nsplit,
+                                           bases, cur, caps, flags, st)
+    assert rc == 0, L.b200sort_last_error()
+    torch.cuda.synchronize()
+    c = ctrl.cpu().numpy()
+    assert c[: nsplit + 1].tolist() == cnt, "the cursors hold the true bucket sizes even for the bucket that overflowed"
+    assert int(c[nsplit + 1]) == 0b0100, "exactly bucket 2 is flagged"
+    pad = np.frombuffer(bytes([fill]) * 8, dtype=a.dtype)[0]
+    for r in range(nsplit + 1):
+        got = regions[r].cpu().numpy()
+        assert _ref.same_bits(got[cap[r]:], np.full(8, pad, dtype=a.dtype)), f"region {r}: a store went past its capacity"
+        if r != 2:
+            assert _ref.same_bits(np.sort(got[: cnt[r]]), np.sort(a[dest == r])), f"region {r}"
+
+
 # ---- full-size runs: size-independent properties (sorted + same multiset) ------------
 
 def _property_run(kind, n, dist, param, cuda, seed=0xB2000002, flags=0):
