@@ -30,7 +30,9 @@ def run_cases(dist, dev, rank, world):
                 continue
             keys = torch.from_numpy(a.copy()).to(dev)
             res = mgpu.sort_sharded(keys, rs.Kind.U64, exchange=exchange if use_exchange else None, overlap=overlap, claim=claim)
-            if claim and case != "overflow":
+            # (few_unique: five distinct values, so one rank's range can legitimately exceed the capacity on >= 4 ranks
+            # and the claim form hands over to the counting form, like "overflow" always does)
+            if claim and case in ("uniform", "ragged"):
                 assert res.send_counts is None, "the claim form must have run (it has no per-sender counts)"
             mine = res.keys.cpu().numpy().copy()
             gathered = [None] * world
