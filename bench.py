@@ -33,6 +33,7 @@ same configuration: N = 1 sorts the whole 1 B-key workload every step.
 from __future__ import annotations
 
 import argparse
+import ctypes
 import json
 import os
 import statistics
@@ -641,6 +642,23 @@ def run_gpu(args):
                 ta.append(time.perf_counter() - t0)
             alloc_inside = {"value": round(n / min(ta) / 1e9, 3), "unit": "Gkeys/s", "ms_per_step": round(min(ta) * 1e3, 3),
                             "note": "device-resident keys; cudaMalloc + cudaFree of the workspace inside the timed region, host wall clock, best of 3"}
+            # the same convention through b200sort_keys_device_pooled: the workspace comes from the library's stream-ordered pool
+            tp_ = []
+            st_ = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            for i in range(4):  # the first call grows the pool
+                keys.copy_(pristine)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                _ffi.check(_ffi.lib().b200sort_keys_device_pooled(keys.data_ptr(), n, int(K), st_))
+                torch.cuda.synchronize()
+                if i > 0:
+                    tp_.append(time.perf_counter() - t0)
+            if verify.count_unsorted(keys, K) != 0 or verify.fingerprint(keys, K) != fp_in:
+                raise SystemExit("pooled-workspace sort failed verification")
+            _ffi.lib().b200sort_release_cached_memory()
+            alloc_inside["pooled"] = {"value": round(n / min(tp_) / 1e9, 3), "unit": "Gkeys/s", "ms_per_step": round(min(tp_) * 1e3, 3),
+                                      "note": "b200sort_keys_device_pooled: workspace taken and returned inside the call from the library's "
+                                              "stream-ordered pool (cudaMallocFromPoolAsync / cudaFreeAsync), host wall clock, best of 3 after the first call"}
             ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         except BaseException as e:  # noqa: BLE001
             note_error("alloc_inside", e)
@@ -846,6 +864,7 @@ def run_gpu(args):
         "e2e_gkeys_s": round(e2e_value, 3) if e2e_value is not None else None,
         "e2e_pageable_gkeys_s": (e2e_pageable or {}).get("value"),
         "alloc_inside_gkeys_s": (alloc_inside or {}).get("value"),
+        "alloc_inside_pooled_gkeys_s": ((alloc_inside or {}).get("pooled") or {}).get("value"),
         "c1_ms": g("C1_10M_u32", "ms"), "c1_host_call_ms": g("C1_10M_u32", "host_call_ms"),
         "c3_f32_gkeys_s": g("C3_1B_f32_test_shaped", "gkeys_s"), "c3_f32_raw_gkeys_s": g("C3_1B_f32_raw_bits", "gkeys_s"),
         "c3_f64_gkeys_s": g("C3_1B_f64_raw_bits", "gkeys_s"), "c3_i32_gkeys_s": g("C3_1B_i32", "gkeys_s"),

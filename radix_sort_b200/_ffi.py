@@ -21,6 +21,7 @@ PROTOTYPES = {
     "b200sort_keys_device": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_int, c_void_p]),
     "b200sort_keys_device_ex": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_int, c_void_p, c_uint]),
     "b200sort_keys_device_noalloc": (c_int, [c_void_p, c_size_t, c_int, c_void_p]),
+    "b200sort_keys_device_pooled": (c_int, [c_void_p, c_size_t, c_int, c_void_p]),
     "b200sort_keys_host": (c_int, [c_void_p, c_size_t, c_int]),
     "b200sort_set_host_pipeline_min_bytes": (c_int, [c_size_t]),
     "b200sort_release_cached_memory": (c_int, []),

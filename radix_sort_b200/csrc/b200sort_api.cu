@@ -472,6 +472,49 @@ int noalloc_scratch_address(void** out) {
 }
 }  // namespace
 
+// ---- stream-ordered workspace pool (b200sort_keys_device_pooled) --------------------------
+// The reference's timer covers the allocation and release of its temp buffer (main.rs:32-34 around
+// mod.rs:71-83, dropped at :176).  cudaMalloc + cudaFree around a 1 B-key sort cost 8.7 ms of 45.7
+// (BENCH_r02 alloc_inside); a stream-ordered allocation from a pool that never gives memory back to the
+// driver costs microseconds after the first call.  One pool per device, owned by the library (the
+// process's default pool and its release threshold are left alone); b200sort_release_cached_memory trims it.
+namespace {
+std::mutex g_wspool_mu;
+cudaMemPool_t g_wspool[NOALLOC_MAX_DEVICES] = {};
+
+int workspace_pool(cudaMemPool_t* out) {
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES)
+        return fail(B200SORT_ERR_INVALID_ARG, "device ordinal " + std::to_string(dev) + " outside the workspace-pool table");
+    std::lock_guard<std::mutex> lk(g_wspool_mu);
+    if (!g_wspool[dev]) {
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        cudaMemPool_t pool = nullptr;
+        CU(cudaMemPoolCreate(&pool, &props));
+        unsigned long long keep = ~0ull;  // freed blocks stay in the pool until it is trimmed
+        const cudaError_t e = cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        if (e != cudaSuccess) {
+            cudaMemPoolDestroy(pool);
+            return cuda_fail(e, "cudaMemPoolSetAttribute(release threshold)");
+        }
+        g_wspool[dev] = pool;
+    }
+    *out = g_wspool[dev];
+    return B200SORT_OK;
+}
+
+void workspace_pools_trim() {
+    std::lock_guard<std::mutex> lk(g_wspool_mu);
+    for (cudaMemPool_t pool : g_wspool)
+        if (pool) cudaMemPoolTrimTo(pool, 0);
+}
+}  // namespace
+
 // ---- exported C ABI ------------------------------------------------------------------
 extern "C" {
 
@@ -535,6 +578,30 @@ int b200sort_keys_device_noalloc(void* d_keys, size_t n, int kind, void* stream)
     return keys_device_dispatch(d_keys, ws, limit, n, kind, static_cast<cudaStream_t>(stream), 0, nullptr, 0);
 }
 
+// Device-resident sort that takes and returns its workspace itself, in stream order (see the pool above):
+// what a caller who would otherwise cudaMalloc / cudaFree around every b200sort_keys_device call should use.
+int b200sort_keys_device_pooled(void* d_keys, size_t n, int kind, void* stream) {
+    const size_t kb = b200sort_key_bytes(kind);
+    if (kb == 0) return fail(B200SORT_ERR_UNSUPPORTED_KIND, "unknown key kind " + std::to_string(kind));
+    if (n == 0) return B200SORT_OK;
+    if (!d_keys) return fail(B200SORT_ERR_INVALID_ARG, "null device pointer");
+    cudaMemPool_t pool = nullptr;
+    if (int rc = workspace_pool(&pool)) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t need = b200sort_temp_bytes(n, kind);
+    void* ws = nullptr;
+    const cudaError_t e = cudaMallocFromPoolAsync(&ws, need, pool, st);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return cuda_fail(e, "cudaMallocFromPoolAsync(workspace)");
+    }
+    const int rc = keys_device_dispatch(d_keys, ws, need, n, kind, st, 0, nullptr, 0);
+    const cudaError_t e2 = cudaFreeAsync(ws, st);  // stream order: after the sort's last kernel
+    if (rc) return rc;
+    if (e2 != cudaSuccess) return cuda_fail(e2, "cudaFreeAsync(workspace)");
+    return B200SORT_OK;
+}
+
 int b200sort_keys_host(void* keys, size_t n, int kind) {
     const size_t kb = b200sort_key_bytes(kind);
     if (kb == 0) return fail(B200SORT_ERR_UNSUPPORTED_KIND, "unknown key kind " + std::to_string(kind));
@@ -564,6 +631,7 @@ int b200sort_release_cached_memory(void) {
         cudaFree(b.p);
     }
     if (prev >= 0) cudaSetDevice(prev);
+    workspace_pools_trim();  // blocks b200sort_keys_device_pooled has returned (work still in flight keeps its own)
     cudaGetLastError();
     return B200SORT_OK;
 }

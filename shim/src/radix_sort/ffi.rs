@@ -39,6 +39,11 @@ extern "C" {
     pub fn b200sort_keys_host(keys: *mut c_void, n: usize, kind: c_int) -> c_int;
     /// device-resident keys, asynchronous on `stream`
     pub fn b200sort_keys_device(d_keys: *mut c_void, d_tmp: *mut c_void, tmp_bytes: usize, n: usize, kind: c_int, stream: *mut c_void) -> c_int;
+    /// device-resident sort with the workspace inside the library image: for hosts like this one, which bind no
+    /// CUDA runtime and so cannot allocate a `d_tmp` (limit: `b200sort_temp_bytes(n, kind)` <= 16 MiB)
+    pub fn b200sort_keys_device_noalloc(d_keys: *mut c_void, n: usize, kind: c_int, stream: *mut c_void) -> c_int;
+    /// device-resident sort whose temp buffer is taken and returned inside the call (library-owned stream-ordered pool)
+    pub fn b200sort_keys_device_pooled(d_keys: *mut c_void, n: usize, kind: c_int, stream: *mut c_void) -> c_int;
     pub fn b200sort_keys_device_ex(d_keys: *mut c_void, d_tmp: *mut c_void, tmp_bytes: usize, n: usize, kind: c_int, stream: *mut c_void, flags: c_uint) -> c_int;
     /// `(K, V)` tuples (radix_digits.rs:126-136): whole records move, stable by the key at `key_off`
     pub fn b200sort_records_temp_bytes(n: usize, rec_bytes: usize, kind: c_int) -> usize;

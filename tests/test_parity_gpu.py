@@ -571,6 +571,30 @@ def test_copyonly_aliases_and_counting_sort(cuda):
         assert _ref.same_bits(c, want)
 
 
+@pytest.mark.parametrize("kind,n", [("u64", 3_000_001), ("f32", 1_000_000), ("i16", 700_000), ("u32", 5000), ("u64", 0)])
+def test_pooled_workspace_entry_point(kind, n, cuda):
+    """b200sort_keys_device_pooled: the temp buffer is taken and returned inside the call (the reference's own
+    convention, mod.rs:71-83,176) from the library's stream-ordered pool.  Same bits as the oracle, call after call;
+    b200sort_release_cached_memory hands the pool's idle memory back and the next call simply allocates again."""
+    import torch
+    L = _ffi.lib()
+    a = _ref.random_keys(kind, n, seed=73)
+    want = a.copy()
+    cpu_oracle.sort0(want, kind)
+    with torch.cuda.device(cuda):
+        st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        for round_ in range(3):
+            t = _to_device(a, cuda) if n else torch.empty(0, dtype=torch.uint64, device=cuda)
+            _ffi.check(L.b200sort_keys_device_pooled(t.data_ptr() if n else None, n, int(_kind(kind)), st))
+            torch.cuda.synchronize()
+            assert _ref.same_bits(t.cpu().numpy(), want), f"{kind}: pooled call {round_} differs from the oracle"
+            if round_ == 1:
+                free_before = torch.cuda.mem_get_info()[0]
+                assert L.b200sort_release_cached_memory() == 0
+                if n >= 700_000:  # the pool held at least the ping-pong buffer of this sort
+                    assert torch.cuda.mem_get_info()[0] > free_before
+
+
 # ---- multi-GPU building block: K7 partition ------------------------------------------
 
 @pytest.mark.parametrize("kind", ["u32", "u64", "i64", "f32"])
@@ -794,6 +818,17 @@ def test_config2_1b_u64_properties(cuda):  # BASELINE.json configs[1]
                                              ("i32", distr.Distr.UNIFORM, 0), ("i64", distr.Distr.UNIFORM, 0)])
 def test_config3_transform_kinds_properties(kind, dist, param, cuda):  # configs[2] at 2^28 keys
     _property_run(kind, 1 << 28, dist, param, cuda)
+
+
+@pytest.mark.parametrize("kind,dist,param", [("f32", distr.Distr.FLOAT_TEST, 0.0), ("f32", distr.Distr.UNIFORM, 0),
+                                             ("f64", distr.Distr.UNIFORM, 0), ("i32", distr.Distr.UNIFORM, 0),
+                                             ("i64", distr.Distr.UNIFORM, 0)],
+                         ids=["f32_test_shaped", "f32_raw_bits", "f64_raw_bits", "i32", "i64"])
+def test_config3_at_its_stated_size_1b_keys(kind, dist, param, cuda):
+    """BASELINE.json configs[2] as stated: 1 000 000 000 keys of each transform kind (radix_digits.rs:55-124), the
+    f32 case on both datasets bench.py times (tests.rs:135-143 shaped: Uniform[-1,1) + specials; and raw bit
+    patterns: every NaN payload, both zeros, subnormals).  Sorted in get_digit's order + same multiset."""
+    _property_run(kind, 1_000_000_000, dist, param, cuda, seed=0xB2000003)
 
 
 @pytest.mark.parametrize("dist,param", [(distr.Distr.ZIPF, 1.0), (distr.Distr.STEP, 16), (distr.Distr.ASCENDING, 2_000_000_000)])
