@@ -76,11 +76,34 @@ hist_values_kernel(const U* __restrict__ in, size_t n, unsigned long long* __res
             if ((v >> 15) == half) atomicAdd(&bins[v & 0x7FFFu], 1u);
         }
     };
+    // The vector loop works on whole 32-bit words: the ordered image of a 1- or 2-byte key is the key with its
+    // sign bit flipped or not (no float kinds at these widths), i.e. ONE xor per word with a mask picked before
+    // the loop, instead of a select per key (r03 ncu digest of the per-key form: issue-bound, 12 ALU instructions
+    // per ATOMS).  u16 folds "is this value in my half" into the same xor: afterwards a key is mine iff its top bit is set.
+    uint32_t wmask;
+    if constexpr (sizeof(U) == 1) wmask = (xf != XF_NONE) ? 0x80808080u : 0u;
+    else wmask = ((xf != XF_NONE) ? 0x80008000u : 0u) ^ (half ? 0u : 0x80008000u);
+    // byte offsets, not indices: (value << 7 | lane << 2) comes out of one shift and one logic op per key, and the
+    // array base rides in the atomic's uniform-register operand
+    unsigned char* const bins_b = reinterpret_cast<unsigned char*>(bins);
+    const uint32_t lane_off = (C::SPLIT == 1) ? (uint32_t)(tid & (C::R - 1)) * 4u : 0u;
+    auto count_word = [&](uint32_t w) {
+        w ^= wmask;
+        if constexpr (sizeof(U) == 1) {
+            static_assert(sizeof(U) != 1 || C::R == 32, "u8: value * 128 + lane * 4");
+            atomicAdd(reinterpret_cast<uint32_t*>(bins_b + (((w << 7) & 0x7F80u) | lane_off)), 1u);
+            atomicAdd(reinterpret_cast<uint32_t*>(bins_b + (((w >> 1) & 0x7F80u) | lane_off)), 1u);
+            atomicAdd(reinterpret_cast<uint32_t*>(bins_b + (((w >> 9) & 0x7F80u) | lane_off)), 1u);
+            atomicAdd(reinterpret_cast<uint32_t*>(bins_b + (((w >> 17) & 0x7F80u) | lane_off)), 1u);
+        } else {
+            // (a predicated `red.shared` does not help: ptxas turns it back into the same branch + warp-aggregated
+            // ATOMS.POPC.INC, and an unconditional add of 0 / 1 would double the shared-memory wavefronts)
+            if (w & 0x8000u) atomicAdd(reinterpret_cast<uint32_t*>(bins_b + ((w << 2) & 0x1FFFCu)), 1u);
+            if (w & 0x80000000u) atomicAdd(reinterpret_cast<uint32_t*>(bins_b + ((w >> 14) & 0x1FFFCu)), 1u);
+        }
+    };
     auto count_vec = [&](uint4 q) {
-        union { uint4 q; U e[VEC]; } u;
-        u.q = q;
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) count(u.e[j]);
+        count_word(q.x); count_word(q.y); count_word(q.z); count_word(q.w);
     };
     const uintptr_t addr = (uintptr_t)in;
     size_t head = ((16 - (addr & 15)) & 15) / sizeof(U);
