@@ -205,7 +205,14 @@ int host_roundtrip(void* host, size_t bytes, size_t ws_bytes, SortFn sort) {
     // large pageable slices (a plain Vec<T>) go through the library's pinned bounce
     // buffers and copy threads (host_staging.cuh); everything else is one DMA each way
     Bounce bounce;
-    const bool staged = bytes >= ((size_t)64 << 20) && is_pageable(host);
+    // (B200SORT_STAGE_MIN_BYTES: sweep knob for where the bounce path starts to beat the driver's own pageable copies)
+    static const size_t stage_min = [] {
+        const char* e = std::getenv("B200SORT_STAGE_MIN_BYTES");
+        // 16 MiB: a 40 MB pageable u32 slice takes 4.6 ms staged against 6.9 ms through the driver's pageable copies; at
+        // 4 MiB an 8 MB slice gets slower (2.2 against 1.35 ms) -- profiles/r03_host_latency_stage_min.jsonl
+        return e ? (size_t)std::strtoull(e, nullptr, 10) : (size_t)16 << 20;
+    }();
+    const bool staged = bytes >= stage_min && is_pageable(host);
     if (staged) e = bounce_acquire(&bounce);
     if (e != cudaSuccess) { pool_release(block); return cuda_fail(e, "cudaHostAlloc(bounce buffers)"); }
     if (staged) {
